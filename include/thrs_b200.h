@@ -1,0 +1,150 @@
+/*
+ * thrs_b200.h — C ABI of the B200-native radix sort (libthrs_b200.so).
+ *
+ * This is the drop-in boundary for the hot path of Ushio/tinyhipradixsort:
+ * everything `thrs::RadixSort` does on the device (reference
+ * tinyhipradixsort.hpp:694-948) is reachable through the plain-C entry points
+ * below.  No C++ types, no torch types, no Orochi types: pointers, sizes and
+ * an opaque stream handle (a `cudaStream_t`, which is what the reference's
+ * `oroStream` is on NVIDIA: libs/Orochi/Orochi/Orochi.cpp:687 is a plain cast).
+ *
+ * All device pointers are CUDA device pointers of the CURRENT device.  Every
+ * function returns 0 on success or a non-zero `thrs_status`; the C++ header
+ * include/tinyhipradixsort.hpp turns non-zero into THRS_ASSERT exactly like
+ * the reference (tinyhipradixsort.hpp:15,856).
+ *
+ * Each entry point cites the reference interface it replaces.
+ */
+#ifndef THRS_B200_H
+#define THRS_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define THRS_API
+#else
+#define THRS_API __attribute__((visibility("default")))
+#endif
+
+/* thrs::KeyType, tinyhipradixsort.hpp:638-644 (same enumerator order). */
+typedef enum thrs_key_type {
+    THRS_KEY_U32 = 0,
+    THRS_KEY_U64 = 1,
+    THRS_KEY_F32 = 2,
+    THRS_KEY_F64 = 3
+} thrs_key_type;
+
+/* thrs::ValueType, tinyhipradixsort.hpp:645-650. */
+typedef enum thrs_value_type {
+    THRS_VALUE_U32 = 0,
+    THRS_VALUE_U64 = 1,
+    THRS_VALUE_U128 = 2
+} thrs_value_type;
+
+/* thrs::SortOrder, tinyhipradixsort.hpp:679-683. */
+typedef enum thrs_sort_order {
+    THRS_ASCENDING = 0,
+    THRS_DESCENDING = 1
+} thrs_sort_order;
+
+typedef enum thrs_status {
+    THRS_OK = 0,
+    THRS_ERR_INVALID_ARGUMENT = 1, /* bad enum, NULL pointer, negative start bit */
+    THRS_ERR_BIT_RANGE = 2,        /* (endBits - startBits) % 8 != 0 (hpp:856) or end < start */
+    THRS_ERR_CUDA = 3,             /* a CUDA runtime call failed; see thrs_last_error() */
+    THRS_ERR_NO_DEVICE = 4,        /* no sm_100 device / no CUDA driver: there is NO CPU fallback */
+    THRS_ERR_ALIGNMENT = 5         /* buffer not aligned to its element size */
+} thrs_status;
+
+/* thrs::RadixSort::Config, tinyhipradixsort.hpp:697-705. */
+typedef struct thrs_config {
+    int32_t key_is_16byte_aligned; /* Config::keyIs16byteAligned (default true) */
+    int32_t key_type;              /* thrs_key_type   */
+    int32_t value_type;            /* thrs_value_type */
+    int32_t sort_order;            /* thrs_sort_order */
+} thrs_config;
+
+/* thrs::RadixSort::TemporaryBufferDef, tinyhipradixsort.hpp:806-832.
+ * Temp layout is [pSumBuffer | keyOutBuffer | valueOutBuffer]; pSumBuffer holds
+ * this library's histograms, tile tickets and look-back status instead of the
+ * reference's 256 x blocks counter matrix.  All three sizes are pure monotone
+ * functions of (n, config) (the reference recomputes them from the sort-time n,
+ * hpp:859) and multiples of 16 bytes. */
+typedef struct thrs_temp_def {
+    uint64_t pSumBuffer;
+    uint64_t keyOutBuffer;
+    uint64_t valueOutBuffer;
+} thrs_temp_def;
+
+typedef struct thrs_sorter thrs_sorter; /* opaque; replaces the Shader/module held by thrs::RadixSort (hpp:945-947) */
+
+/* Fills *cfg with the reference defaults (hpp:699-705). */
+THRS_API void thrs_config_default(thrs_config* cfg);
+
+/* thrs::RadixSort::RadixSort(extraArgs, config), hpp:751-804.  Selects precompiled
+ * sm_100a kernels for the (key, value, order) triple; nothing is JIT-compiled. */
+THRS_API int thrs_create(const thrs_config* cfg, thrs_sorter** out);
+THRS_API void thrs_destroy(thrs_sorter* s);
+
+/* thrs::RadixSort::getTemporaryBufferBytes(n), hpp:833-843. Pure host arithmetic. */
+THRS_API int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out);
+
+/* thrs::RadixSort::sortKeys, hpp:845-848.  Stable LSD sort of `n` keys on bits
+ * [start_bits, end_bits) of getKeyBits(key) (fpKey.hpp:15-38, kernel.cu:46-69);
+ * result is in `keys`; asynchronous on `stream` (a cudaStream_t, may be NULL). */
+THRS_API int thrs_sort_keys(thrs_sorter* s, void* keys, uint32_t n, void* temp,
+                            int start_bits, int end_bits, void* stream);
+
+/* thrs::RadixSort::sortPairs, hpp:849-852. */
+THRS_API int thrs_sort_pairs(thrs_sorter* s, void* keys, void* values, uint32_t n, void* temp,
+                             int start_bits, int end_bits, void* stream);
+
+/* Host-buffer convenience used for end-to-end timing: what unittest.cpp:399-414
+ * does around a sort (thrs::Buffer alloc, H2D, sort, sync, D2H), in one call.
+ * `values` may be NULL for a keys-only sort.  Blocking. */
+THRS_API int thrs_sort_host(thrs_sorter* s, void* host_keys, void* host_values, uint32_t n,
+                            int start_bits, int end_bits);
+
+/* Host getKeyBits family, fpKey.hpp:15-38 (ascending order function). */
+THRS_API uint32_t thrs_key_bits_u32(uint32_t x);
+THRS_API uint64_t thrs_key_bits_u64(uint64_t x);
+THRS_API uint32_t thrs_key_bits_f32(uint32_t float_bits);
+THRS_API uint64_t thrs_key_bits_f64(uint64_t double_bits);
+
+/* thrs::Buffer, hpp:501-528: cudaMalloc(max(bytes,1)) / cudaFree on the current device. */
+THRS_API int thrs_buffer_alloc(int64_t bytes, void** out_device_ptr);
+THRS_API int thrs_buffer_free(void* device_ptr);
+
+/* Per-stage device timing with CUDA events recorded on the caller's stream between the
+ * launches of a sort (the role of the commented-out OroStopwatch blocks in hpp:882-928).
+ * While enabled, keep one sort in flight per sorter.  thrs_profile_read blocks until the
+ * last profiled sort finished. */
+typedef struct thrs_profile {
+    float memset_ms;    /* scratch clear                      */
+    float histogram_ms; /* histogram_kernel                   */
+    float pass_ms[8];   /* onesweep_kernel launches of pass i */
+    float copyback_ms;  /* odd pass count only                */
+    float total_ms;
+    int32_t passes;
+    int32_t parts;      /* onesweep launches per pass         */
+} thrs_profile;
+THRS_API int thrs_profile_enable(thrs_sorter* s, int on);
+THRS_API int thrs_profile_read(thrs_sorter* s, thrs_profile* out);
+
+/* Diagnostics. */
+THRS_API const char* thrs_last_error(void);        /* thread-local text of the last failure */
+THRS_API const char* thrs_version(void);
+/* Number of kernels the last thrs_sort_* call on this thread enqueued (bench.py's gpu_launches). */
+THRS_API int thrs_last_launch_count(void);
+/* Items per onesweep tile for this sorter (test/bench introspection). */
+THRS_API uint32_t thrs_tile_items(const thrs_sorter* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* THRS_B200_H */

@@ -1,0 +1,89 @@
+"""ctypes binding of the C ABI (include/thrs_b200.h) — libthrs_b200.so, built in-tree by
+``tinyhipradixsort_b200/csrc/Makefile`` (``__graft_entry__.build()``).
+
+There is deliberately no fallback: if the shared library is missing the import of the
+sort fails loudly, and if no CUDA device is usable every sort call raises.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libthrs_b200.so")
+
+
+class thrs_config(ctypes.Structure):
+    _fields_ = [
+        ("key_is_16byte_aligned", ctypes.c_int32),
+        ("key_type", ctypes.c_int32),
+        ("value_type", ctypes.c_int32),
+        ("sort_order", ctypes.c_int32),
+    ]
+
+
+class thrs_temp_def(ctypes.Structure):
+    _fields_ = [
+        ("pSumBuffer", ctypes.c_uint64),
+        ("keyOutBuffer", ctypes.c_uint64),
+        ("valueOutBuffer", ctypes.c_uint64),
+    ]
+
+
+class thrs_profile(ctypes.Structure):
+    _fields_ = [
+        ("memset_ms", ctypes.c_float),
+        ("histogram_ms", ctypes.c_float),
+        ("pass_ms", ctypes.c_float * 8),
+        ("copyback_ms", ctypes.c_float),
+        ("total_ms", ctypes.c_float),
+        ("passes", ctypes.c_int32),
+        ("parts", ctypes.c_int32),
+    ]
+
+
+# name -> (restype, argtypes); must list every symbol include/thrs_b200.h declares
+# (tests/test_abi.py checks the two against each other).
+SIGNATURES = {
+    "thrs_config_default": (None, [ctypes.POINTER(thrs_config)]),
+    "thrs_create": (ctypes.c_int, [ctypes.POINTER(thrs_config), ctypes.POINTER(ctypes.c_void_p)]),
+    "thrs_destroy": (None, [ctypes.c_void_p]),
+    "thrs_temp_bytes": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(thrs_temp_def)]),
+    "thrs_sort_keys": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p,
+                                      ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
+    "thrs_sort_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
+                                       ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
+    "thrs_sort_host": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
+                                      ctypes.c_int, ctypes.c_int]),
+    "thrs_key_bits_u32": (ctypes.c_uint32, [ctypes.c_uint32]),
+    "thrs_key_bits_u64": (ctypes.c_uint64, [ctypes.c_uint64]),
+    "thrs_key_bits_f32": (ctypes.c_uint32, [ctypes.c_uint32]),
+    "thrs_key_bits_f64": (ctypes.c_uint64, [ctypes.c_uint64]),
+    "thrs_buffer_alloc": (ctypes.c_int, [ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]),
+    "thrs_buffer_free": (ctypes.c_int, [ctypes.c_void_p]),
+    "thrs_profile_enable": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "thrs_profile_read": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(thrs_profile)]),
+    "thrs_last_error": (ctypes.c_char_p, []),
+    "thrs_version": (ctypes.c_char_p, []),
+    "thrs_last_launch_count": (ctypes.c_int, []),
+    "thrs_tile_items": (ctypes.c_uint32, [ctypes.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Load libthrs_b200.so (once) and attach prototypes.  Raises if it was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `make -C tinyhipradixsort_b200/csrc` "
+            "(or __graft_entry__.build()). There is no CPU or PyTorch fallback."
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export it
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib

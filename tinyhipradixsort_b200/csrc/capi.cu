@@ -1,0 +1,358 @@
+// capi.cu — the C ABI (include/thrs_b200.h) and the host driver of the sort.
+//
+// Host-side counterpart of thrs::RadixSort::sort (reference tinyhipradixsort.hpp:854-944):
+// same contract (bits [start,end) in 8-bit steps, stable, result in the caller's buffers,
+// caller-owned temp carved as [pSum | keyOut | valueOut], asynchronous on the caller's
+// stream) but a different schedule: 1 memset + 1 histogram launch + 1 onesweep launch per
+// pass (+ an async copy-back when the pass count is odd) instead of 3 launches per pass.
+// Calls the CUDA runtime directly: no Orochi, no NVRTC, no CPU fallback.
+#include <cuda_runtime.h>
+#include <mutex>
+#include <new>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/thrs_b200.h"
+#include "launch.cuh"
+
+using namespace thrs_b200;
+
+namespace {
+
+thread_local char g_err[512] = "";
+thread_local int g_launches = 0;
+
+int fail(int code, const char* fmt, const char* a = "", const char* b = "")
+{
+    snprintf(g_err, sizeof(g_err), fmt, a, b);
+    return code;
+}
+int fail_cuda(cudaError_t e, const char* what)
+{
+    return fail(THRS_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+#define CUDA_TRY(expr, what)                                \
+    do {                                                    \
+        cudaError_t e__ = (expr);                           \
+        if (e__ != cudaSuccess) return fail_cuda(e__, what); \
+    } while (0)
+
+inline uint64_t align16(uint64_t x) { return (x + 15ull) & ~15ull; }
+inline uint64_t div_up(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+int key_bytes(int kt) { return (kt == THRS_KEY_U32 || kt == THRS_KEY_F32) ? 4 : 8; }
+int value_bytes(int vt) { return vt == THRS_VALUE_U32 ? 4 : (vt == THRS_VALUE_U64 ? 8 : 16); }
+int value_slot(int vt) { return vt == THRS_VALUE_U32 ? 1 : (vt == THRS_VALUE_U64 ? 2 : 3); }
+
+} // namespace
+
+struct thrs_sorter {
+    thrs_config cfg;
+    const KernelTable* table;
+    int kbytes;
+    int vbytes;
+    int vslot;
+    // lazily initialised per process (first sort): device facts + smem opt-in
+    std::once_flag prepared_once;
+    cudaError_t prepared_err = cudaSuccess;
+    int sm_count = 148;
+    // workspace of thrs_sort_host (grown on demand, guarded)
+    std::mutex host_mu;
+    void* ws_keys = nullptr;
+    void* ws_vals = nullptr;
+    void* ws_temp = nullptr;
+    uint64_t ws_keys_bytes = 0, ws_vals_bytes = 0, ws_temp_bytes = 0;
+    cudaStream_t ws_stream = nullptr;
+    // optional per-stage CUDA-event timing (thrs_profile_enable); one sort in flight when on
+    bool profiling = false;
+    cudaEvent_t ev[MAX_PASSES * MAX_PARTS + 4] = {};
+    int ev_count = 0;       // events recorded by the last sort
+    int ev_passes = 0;      // passes of the last sort
+    int ev_parts = 0;
+    bool ev_copyback = false;
+};
+
+extern "C" {
+
+void thrs_config_default(thrs_config* cfg)
+{
+    if (!cfg) return;
+    cfg->key_is_16byte_aligned = 1;
+    cfg->key_type = THRS_KEY_U32;
+    cfg->value_type = THRS_VALUE_U32;
+    cfg->sort_order = THRS_ASCENDING;
+}
+
+int thrs_create(const thrs_config* cfg, thrs_sorter** out)
+{
+    if (!cfg || !out) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_create: NULL argument");
+    if (cfg->key_type < THRS_KEY_U32 || cfg->key_type > THRS_KEY_F64)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_create: bad key_type");
+    if (cfg->value_type < THRS_VALUE_U32 || cfg->value_type > THRS_VALUE_U128)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_create: bad value_type");
+    if (cfg->sort_order != THRS_ASCENDING && cfg->sort_order != THRS_DESCENDING)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_create: bad sort_order");
+    thrs_sorter* s = new (std::nothrow) thrs_sorter();
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_create: out of host memory");
+    s->cfg = *cfg;
+    const bool desc = cfg->sort_order == THRS_DESCENDING;
+    switch (cfg->key_type) {
+    case THRS_KEY_U32: s->table = table_u32(desc); break;
+    case THRS_KEY_U64: s->table = table_u64(desc); break;
+    case THRS_KEY_F32: s->table = table_f32(desc); break;
+    default: s->table = table_f64(desc); break;
+    }
+    s->kbytes = key_bytes(cfg->key_type);
+    s->vbytes = value_bytes(cfg->value_type);
+    s->vslot = value_slot(cfg->value_type);
+    *out = s;
+    return THRS_OK;
+}
+
+void thrs_destroy(thrs_sorter* s)
+{
+    if (!s) return;
+    if (s->ws_keys) cudaFree(s->ws_keys);
+    if (s->ws_vals) cudaFree(s->ws_vals);
+    if (s->ws_temp) cudaFree(s->ws_temp);
+    if (s->ws_stream) cudaStreamDestroy(s->ws_stream);
+    for (cudaEvent_t e : s->ev)
+        if (e) cudaEventDestroy(e);
+    delete s;
+}
+
+uint32_t thrs_tile_items(const thrs_sorter* s) { return s ? s->table->tile_items[s->vslot] : 0; }
+
+int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out)
+{
+    if (!s || !out) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_temp_bytes: NULL argument");
+    // One layout serves sortKeys and sortPairs of this sorter: size the status rows for
+    // the smaller of the two tile shapes.  Pure, monotone function of n (hpp:859).
+    const uint32_t t_keys = s->table->tile_items[0];
+    const uint32_t t_pairs = s->table->tile_items[s->vslot];
+    const uint64_t tiles = div_up(n, t_keys < t_pairs ? t_keys : t_pairs);
+    const uint64_t passes = (uint64_t)s->kbytes; // key bits / 8
+    out->pSumBuffer = align16(4ull * (Scratch::CONTROL_WORDS + passes * tiles * RADIX));
+    out->keyOutBuffer = align16((uint64_t)s->kbytes * n);
+    out->valueOutBuffer = align16((uint64_t)s->vbytes * n);
+    return THRS_OK;
+}
+
+static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint32_t n, void* temp, int start_bits,
+                     int end_bits, cudaStream_t stream)
+{
+    g_launches = 0;
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "sort: NULL sorter");
+    if (start_bits < 0 || end_bits < start_bits)
+        return fail(THRS_ERR_BIT_RANGE, "sort: need 0 <= startBits <= endBits");
+    if (((end_bits - start_bits) % 8) != 0)
+        return fail(THRS_ERR_BIT_RANGE, "sort: (endBits - startBits) must be a multiple of 8");
+    if (n == 0 || start_bits == end_bits) return THRS_OK;
+    if (!keys || !temp || (pairs && !values)) return fail(THRS_ERR_INVALID_ARGUMENT, "sort: NULL buffer");
+    if (((uintptr_t)keys % s->kbytes) != 0 || ((uintptr_t)temp % 16) != 0 ||
+        (pairs && ((uintptr_t)values % s->vbytes) != 0))
+        return fail(THRS_ERR_ALIGNMENT, "sort: misaligned buffer");
+
+    // Passes that start at or beyond the key width see digit 0 everywhere (zero extension,
+    // keybits.cuh): a stable pass is then the identity and is skipped.
+    const int key_bits = s->kbytes * 8;
+    int passes = 0;
+    for (int b = start_bits; b < end_bits && b < key_bits; b += 8) ++passes;
+    if (passes == 0) return THRS_OK;
+
+    std::call_once(s->prepared_once, [s]() {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, dev);
+        for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[v]();
+        s->prepared_err = e;
+    });
+    if (s->prepared_err != cudaSuccess) {
+        cudaGetLastError();
+        return fail(THRS_ERR_NO_DEVICE, "no usable CUDA device (%s); this library has no CPU fallback",
+                    cudaGetErrorString(s->prepared_err));
+    }
+
+    thrs_temp_def def;
+    thrs_temp_bytes(s, n, &def);
+    Scratch sc{static_cast<uint32_t*>(temp)};
+    char* key_out = static_cast<char*>(temp) + def.pSumBuffer;
+    char* val_out = key_out + def.keyOutBuffer;
+
+    const int vslot = pairs ? s->vslot : 0;
+    const uint32_t tile = s->table->tile_items[vslot];
+    const uint64_t tiles_total = div_up(n, tile);
+    const uint64_t part_items = (uint64_t)(VALUE_MASK / tile) * tile; // < 2^30, whole tiles
+    const int parts = (int)div_up(n, part_items);
+    if (parts > MAX_PARTS) return fail(THRS_ERR_INVALID_ARGUMENT, "sort: too many parts");
+
+    int ev_i = 0;
+    auto mark = [&]() -> cudaError_t {
+        if (!s->profiling) return cudaSuccess;
+        if (!s->ev[ev_i]) {
+            cudaError_t e = cudaEventCreate(&s->ev[ev_i]);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaEventRecord(s->ev[ev_i++], stream);
+    };
+    CUDA_TRY(mark(), "profile event");
+
+    // zero: histograms, bases, tickets, counters and the status rows of the passes we run
+    const size_t clear_bytes = 4ull * (Scratch::CONTROL_WORDS + (uint64_t)passes * tiles_total * RADIX);
+    CUDA_TRY(cudaMemsetAsync(temp, 0, clear_bytes, stream), "cudaMemsetAsync(scratch)");
+    CUDA_TRY(mark(), "profile event");
+
+    {
+        const uint64_t vec_per_block = (uint64_t)HIST_THREADS * 2;
+        const uint64_t nvec = (uint64_t)n * s->kbytes / 16;
+        uint64_t grid = div_up(nvec > 0 ? nvec : 1, vec_per_block);
+        const uint64_t cap = (uint64_t)s->sm_count * 4; // 4 x 512 threads resident per SM
+        if (grid > cap) grid = cap;
+        CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bits, passes, sc, (int)grid, stream),
+                 "histogram_kernel launch");
+        ++g_launches;
+        CUDA_TRY(mark(), "profile event");
+    }
+
+    char* k_in = static_cast<char*>(keys);
+    char* k_out = key_out;
+    char* v_in = static_cast<char*>(values);
+    char* v_out = val_out;
+    for (int p = 0; p < passes; ++p) {
+        for (int q = 0; q < parts; ++q) {
+            const uint64_t first = (uint64_t)q * part_items;
+            const uint64_t count = (n - first) < part_items ? (n - first) : part_items;
+            OnesweepArgs a;
+            a.keys_in = k_in + first * s->kbytes;
+            a.keys_out = k_out;
+            a.vals_in = pairs ? v_in + first * s->vbytes : nullptr;
+            a.vals_out = pairs ? v_out : nullptr;
+            a.n = (uint32_t)count;
+            a.bit = (uint32_t)(start_bits + 8 * p);
+            a.status = sc.status(p, tiles_total) + (first / tile) * RADIX;
+            a.ticket = sc.ticket(p, q);
+            a.base_in = sc.base(p, q);
+            a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;
+            CUDA_TRY(s->table->onesweep[vslot](a, stream), "onesweep_kernel launch");
+            ++g_launches;
+        }
+        CUDA_TRY(mark(), "profile event");
+        char* t = k_in; k_in = k_out; k_out = t;
+        t = v_in; v_in = v_out; v_out = t;
+    }
+    if (passes & 1) {
+        // result must land in the caller's buffers (hpp:936-943); on the caller's stream
+        CUDA_TRY(cudaMemcpyAsync(keys, key_out, (size_t)s->kbytes * n, cudaMemcpyDeviceToDevice, stream),
+                 "copy-back keys");
+        if (pairs)
+            CUDA_TRY(cudaMemcpyAsync(values, val_out, (size_t)s->vbytes * n, cudaMemcpyDeviceToDevice, stream),
+                     "copy-back values");
+        CUDA_TRY(mark(), "profile event");
+    }
+    s->ev_count = ev_i;
+    s->ev_passes = passes;
+    s->ev_parts = parts;
+    s->ev_copyback = (passes & 1) != 0;
+    return THRS_OK;
+}
+
+int thrs_sort_keys(thrs_sorter* s, void* keys, uint32_t n, void* temp, int start_bits, int end_bits, void* stream)
+{
+    return sort_impl(s, keys, nullptr, false, n, temp, start_bits, end_bits, static_cast<cudaStream_t>(stream));
+}
+
+int thrs_sort_pairs(thrs_sorter* s, void* keys, void* values, uint32_t n, void* temp, int start_bits, int end_bits,
+                    void* stream)
+{
+    return sort_impl(s, keys, values, true, n, temp, start_bits, end_bits, static_cast<cudaStream_t>(stream));
+}
+
+static int grow(void** p, uint64_t* have, uint64_t need)
+{
+    if (*have >= need && *p) return THRS_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *have = 0;
+    CUDA_TRY(cudaMalloc(p, need ? need : 1), "cudaMalloc(workspace)");
+    *have = need;
+    return THRS_OK;
+}
+
+int thrs_sort_host(thrs_sorter* s, void* host_keys, void* host_values, uint32_t n, int start_bits, int end_bits)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host: NULL sorter");
+    if (n == 0) return THRS_OK;
+    if (!host_keys) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host: NULL keys");
+    std::lock_guard<std::mutex> lock(s->host_mu);
+    const bool pairs = host_values != nullptr;
+    thrs_temp_def def;
+    thrs_temp_bytes(s, n, &def);
+    const uint64_t kb = (uint64_t)s->kbytes * n, vb = (uint64_t)s->vbytes * n;
+    int rc;
+    if ((rc = grow(&s->ws_keys, &s->ws_keys_bytes, kb))) return rc;
+    if (pairs && (rc = grow(&s->ws_vals, &s->ws_vals_bytes, vb))) return rc;
+    if ((rc = grow(&s->ws_temp, &s->ws_temp_bytes,
+                   def.pSumBuffer + def.keyOutBuffer + (pairs ? def.valueOutBuffer : 0))))
+        return rc;
+    if (!s->ws_stream) CUDA_TRY(cudaStreamCreateWithFlags(&s->ws_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    cudaStream_t st = s->ws_stream;
+    CUDA_TRY(cudaMemcpyAsync(s->ws_keys, host_keys, kb, cudaMemcpyHostToDevice, st), "H2D keys");
+    if (pairs) CUDA_TRY(cudaMemcpyAsync(s->ws_vals, host_values, vb, cudaMemcpyHostToDevice, st), "H2D values");
+    rc = sort_impl(s, s->ws_keys, pairs ? s->ws_vals : nullptr, pairs, n, s->ws_temp, start_bits, end_bits, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(host_keys, s->ws_keys, kb, cudaMemcpyDeviceToHost, st), "D2H keys");
+    if (pairs) CUDA_TRY(cudaMemcpyAsync(host_values, s->ws_vals, vb, cudaMemcpyDeviceToHost, st), "D2H values");
+    CUDA_TRY(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    return THRS_OK;
+}
+
+uint32_t thrs_key_bits_u32(uint32_t x) { return key_bits32<0, false>(x); }
+uint64_t thrs_key_bits_u64(uint64_t x) { return key_bits64<0, false>(x); }
+uint32_t thrs_key_bits_f32(uint32_t b) { return key_bits32<1, false>(b); }
+uint64_t thrs_key_bits_f64(uint64_t b) { return key_bits64<1, false>(b); }
+
+int thrs_buffer_alloc(int64_t bytes, void** out)
+{
+    if (!out) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_buffer_alloc: NULL out");
+    *out = nullptr;
+    CUDA_TRY(cudaMalloc(out, (size_t)(bytes > 1 ? bytes : 1)), "cudaMalloc");
+    return THRS_OK;
+}
+int thrs_buffer_free(void* p)
+{
+    CUDA_TRY(cudaFree(p), "cudaFree");
+    return THRS_OK;
+}
+
+int thrs_profile_enable(thrs_sorter* s, int on)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_profile_enable: NULL sorter");
+    s->profiling = on != 0;
+    s->ev_count = 0;
+    return THRS_OK;
+}
+
+int thrs_profile_read(thrs_sorter* s, thrs_profile* out)
+{
+    if (!s || !out) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_profile_read: NULL argument");
+    memset(out, 0, sizeof(*out));
+    if (!s->profiling || s->ev_count < 3) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_profile_read: no profiled sort");
+    CUDA_TRY(cudaEventSynchronize(s->ev[s->ev_count - 1]), "cudaEventSynchronize");
+    int i = 0;
+    CUDA_TRY(cudaEventElapsedTime(&out->memset_ms, s->ev[i], s->ev[i + 1]), "cudaEventElapsedTime"); ++i;
+    CUDA_TRY(cudaEventElapsedTime(&out->histogram_ms, s->ev[i], s->ev[i + 1]), "cudaEventElapsedTime"); ++i;
+    out->passes = s->ev_passes;
+    out->parts = s->ev_parts;
+    for (int p = 0; p < s->ev_passes; ++p, ++i)
+        CUDA_TRY(cudaEventElapsedTime(&out->pass_ms[p], s->ev[i], s->ev[i + 1]), "cudaEventElapsedTime");
+    if (s->ev_copyback) CUDA_TRY(cudaEventElapsedTime(&out->copyback_ms, s->ev[i], s->ev[i + 1]), "cudaEventElapsedTime");
+    CUDA_TRY(cudaEventElapsedTime(&out->total_ms, s->ev[0], s->ev[s->ev_count - 1]), "cudaEventElapsedTime");
+    return THRS_OK;
+}
+
+const char* thrs_last_error(void) { return g_err; }
+const char* thrs_version(void) { return "thrs_b200 0.1 (sm_100a onesweep)"; }
+int thrs_last_launch_count(void) { return g_launches; }
+
+} // extern "C"

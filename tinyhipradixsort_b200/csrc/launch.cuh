@@ -1,0 +1,94 @@
+// launch.cuh — typed launchers behind an untyped function table, so the C ABI
+// (capi.cu) can pick the precompiled sm_100a instantiation that the reference would
+// have JIT-compiled from -DRADIX_SORT_KEY_TYPE / -DRADIX_SORT_VALUE_TYPE /
+// -DDESCENDING_ORDER (tinyhipradixsort.hpp:754-791).
+#pragma once
+#include "kernels.cuh"
+
+namespace thrs_b200 {
+
+// Tile shape per (key bytes, value bytes).  THREADS x ITEMS items per tile.
+template <int KBYTES, int VBYTES> struct Tuning { static constexpr int THREADS = 512, ITEMS = 16; };
+template <> struct Tuning<4, 8> { static constexpr int THREADS = 512, ITEMS = 12; };
+template <> struct Tuning<4, 16> { static constexpr int THREADS = 512, ITEMS = 8; };
+template <> struct Tuning<8, 0> { static constexpr int THREADS = 512, ITEMS = 12; };
+template <> struct Tuning<8, 4> { static constexpr int THREADS = 512, ITEMS = 12; };
+template <> struct Tuning<8, 8> { static constexpr int THREADS = 512, ITEMS = 12; };
+template <> struct Tuning<8, 16> { static constexpr int THREADS = 512, ITEMS = 8; };
+
+struct OnesweepArgs {
+    const void* keys_in;
+    void* keys_out;
+    const void* vals_in;
+    void* vals_out;
+    uint32_t n;   // items of this part
+    uint32_t bit; // first bit of the digit
+    uint32_t* status;
+    uint32_t* ticket;
+    const uint32_t* base_in;
+    uint32_t* base_out;
+};
+
+struct KernelTable {
+    // value slot: 0 = keys only, 1 = 4-byte, 2 = 8-byte, 3 = 16-byte values
+    cudaError_t (*histogram)(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
+                             cudaStream_t stream);
+    cudaError_t (*onesweep[4])(const OnesweepArgs& a, cudaStream_t stream);
+    cudaError_t (*prepare[4])(); // opt in to > 48 KiB dynamic shared memory
+    uint32_t tile_items[4];
+};
+
+template <class KeyT, int KIND, bool DESC>
+cudaError_t launch_histogram(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
+                             cudaStream_t stream)
+{
+    histogram_kernel<KeyT, KIND, DESC>
+        <<<grid, HIST_THREADS, 0, stream>>>(static_cast<const KeyT*>(keys), n, start_bit, passes, sc);
+    return cudaGetLastError();
+}
+
+template <class KeyT, int KIND, bool DESC, int VBYTES>
+cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
+{
+    using T = Tuning<(int)sizeof(KeyT), VBYTES>;
+    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS>;
+    using ValT = typename ValueOf<VBYTES>::type;
+    const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
+    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS><<<tiles, T::THREADS, SM::BYTES, stream>>>(
+        static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
+        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.status, a.ticket, a.base_in, a.base_out);
+    return cudaGetLastError();
+}
+
+template <class KeyT, int KIND, bool DESC, int VBYTES>
+cudaError_t prepare_onesweep()
+{
+    using T = Tuning<(int)sizeof(KeyT), VBYTES>;
+    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS>;
+    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES);
+}
+
+template <class KeyT, int KIND, bool DESC>
+const KernelTable* make_table()
+{
+    static const KernelTable t = {
+        &launch_histogram<KeyT, KIND, DESC>,
+        {&launch_onesweep<KeyT, KIND, DESC, 0>, &launch_onesweep<KeyT, KIND, DESC, 4>,
+         &launch_onesweep<KeyT, KIND, DESC, 8>, &launch_onesweep<KeyT, KIND, DESC, 16>},
+        {&prepare_onesweep<KeyT, KIND, DESC, 0>, &prepare_onesweep<KeyT, KIND, DESC, 4>,
+         &prepare_onesweep<KeyT, KIND, DESC, 8>, &prepare_onesweep<KeyT, KIND, DESC, 16>},
+        {(uint32_t)(Tuning<(int)sizeof(KeyT), 0>::THREADS * Tuning<(int)sizeof(KeyT), 0>::ITEMS),
+         (uint32_t)(Tuning<(int)sizeof(KeyT), 4>::THREADS * Tuning<(int)sizeof(KeyT), 4>::ITEMS),
+         (uint32_t)(Tuning<(int)sizeof(KeyT), 8>::THREADS * Tuning<(int)sizeof(KeyT), 8>::ITEMS),
+         (uint32_t)(Tuning<(int)sizeof(KeyT), 16>::THREADS * Tuning<(int)sizeof(KeyT), 16>::ITEMS)}};
+    return &t;
+}
+
+// one translation unit per key type (parallel nvcc): inst_u32.cu ... inst_f64.cu
+const KernelTable* table_u32(bool desc);
+const KernelTable* table_u64(bool desc);
+const KernelTable* table_f32(bool desc);
+const KernelTable* table_f64(bool desc);
+
+} // namespace thrs_b200
