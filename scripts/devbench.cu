@@ -1,0 +1,111 @@
+// devbench.cu — developer benchmark on the GPU box (not product, not the judged bench.py):
+// times libthrs_b200.so through its C ABI with per-stage CUDA events, checks the result
+// bit-for-bit on the device against cub::DeviceRadixSort (stable) and prints CUB's time as
+// the comparator the reference author also used (cudaEnv.cu:85-116).
+//   devbench [log2n=28] [pairs=1] [dist=uniform|equal|range16|unique8|window] [reps=5] [cub=1]
+#include <cub/cub.cuh>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include "../include/thrs_b200.h"
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
+
+__device__ __forceinline__ uint64_t mix(uint64_t i)
+{
+    uint64_t z = (i + 1) * 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+__global__ void gen(uint32_t* k, uint32_t* v, uint32_t n, int dist)
+{
+    const uint32_t t8[8] = {0xDEADBEEFu, 0u, 0xFFFFFFFFu, 0x80000000u, 0x00010000u, 0x12345678u, 0x00FF00FFu, 0x7FFFFFFFu};
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint32_t x = (uint32_t)mix(i);
+        if (dist == 1) x = 0xDEADBEEFu;
+        else if (dist == 2) x &= 0xFFFFu;
+        else if (dist == 3) x = t8[x & 7];
+        k[i] = x;
+        if (v) v[i] = (uint32_t)i;
+    }
+}
+__global__ void diff(const uint32_t* a, const uint32_t* b, uint32_t n, unsigned long long* cnt)
+{
+    unsigned long long c = 0;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) c += a[i] != b[i];
+    if (c) atomicAdd(cnt, c);
+}
+
+int main(int argc, char** argv)
+{
+    int log2n = argc > 1 ? atoi(argv[1]) : 28;
+    int pairs = argc > 2 ? atoi(argv[2]) : 1;
+    const char* dname = argc > 3 ? argv[3] : "uniform";
+    int reps = argc > 4 ? atoi(argv[4]) : 5;
+    int use_cub = argc > 5 ? atoi(argv[5]) : 1;
+    int dist = !strcmp(dname, "equal") ? 1 : !strcmp(dname, "range16") ? 2 : !strcmp(dname, "unique8") ? 3 : 0;
+    int sb = 0, eb = 32;
+    if (!strcmp(dname, "window")) { sb = 8; eb = 24; }
+    uint32_t n = log2n >= 32 ? 0xffffffffu : (1u << log2n);
+    if (argc > 6) n = (uint32_t)strtoull(argv[6], 0, 10);
+    size_t kb = (size_t)n * 4;
+    uint32_t *k0, *v0 = 0, *k, *v = 0, *ck, *cv = 0, *ck2 = 0, *cv2 = 0;
+    CK(cudaMalloc(&k0, kb)); CK(cudaMalloc(&k, kb)); CK(cudaMalloc(&ck, kb));
+    if (pairs) { CK(cudaMalloc(&v0, kb)); CK(cudaMalloc(&v, kb)); CK(cudaMalloc(&cv, kb)); }
+    gen<<<148 * 8, 256>>>(k0, v0, n, dist);
+    CK(cudaDeviceSynchronize());
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    float cub_ms = 0;
+    if (use_cub) {
+        CK(cudaMalloc(&ck2, kb)); if (pairs) CK(cudaMalloc(&cv2, kb));
+        void* tmp = 0; size_t tb = 0;
+        if (pairs) cub::DeviceRadixSort::SortPairs(tmp, tb, k0, ck, v0, cv, n, sb, eb);
+        else cub::DeviceRadixSort::SortKeys(tmp, tb, k0, ck, n, sb, eb);
+        CK(cudaMalloc(&tmp, tb));
+        float best = 1e9;
+        for (int r = 0; r < 3; ++r) {
+            CK(cudaEventRecord(e0));
+            if (pairs) cub::DeviceRadixSort::SortPairs(tmp, tb, k0, ck, v0, cv, n, sb, eb);
+            else cub::DeviceRadixSort::SortKeys(tmp, tb, k0, ck, n, sb, eb);
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+            float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); if (ms < best) best = ms;
+        }
+        cub_ms = best;
+        CK(cudaFree(tmp));
+    }
+    thrs_config cfg; thrs_config_default(&cfg);
+    thrs_sorter* s; if (thrs_create(&cfg, &s)) { printf("create: %s\n", thrs_last_error()); return 1; }
+    thrs_temp_def def; thrs_temp_bytes(s, n, &def);
+    void* temp; CK(cudaMalloc(&temp, def.pSumBuffer + def.keyOutBuffer + (pairs ? def.valueOutBuffer : 0)));
+    thrs_profile_enable(s, 1);
+    thrs_profile best; best.total_ms = 1e9f;
+    for (int r = 0; r < reps + 2; ++r) {
+        CK(cudaMemcpy(k, k0, kb, cudaMemcpyDeviceToDevice));
+        if (pairs) CK(cudaMemcpy(v, v0, kb, cudaMemcpyDeviceToDevice));
+        int rc = pairs ? thrs_sort_pairs(s, k, v, n, temp, sb, eb, 0) : thrs_sort_keys(s, k, n, temp, sb, eb, 0);
+        if (rc) { printf("sort failed: %s\n", thrs_last_error()); return 1; }
+        thrs_profile p; if (thrs_profile_read(s, &p)) { printf("profile: %s\n", thrs_last_error()); return 1; }
+        if (r >= 2 && p.total_ms < best.total_ms) best = p;
+    }
+    CK(cudaDeviceSynchronize());
+    int passes = (eb - sb) / 8;
+    double bytes = (double)n * 4 + (double)passes * 2 * n * (pairs ? 8 : 4);
+    printf("n=%u pairs=%d dist=%s bits[%d,%d): thrs %.3f ms (memset %.3f hist %.3f passes", n, pairs, dname, sb, eb,
+           best.total_ms, best.memset_ms, best.histogram_ms);
+    for (int p = 0; p < best.passes; ++p) printf(" %.3f", best.pass_ms[p]);
+    printf(") %.2f Gkeys/s %.0f GB/s-alg", n / best.total_ms / 1e6, bytes / best.total_ms / 1e6);
+    if (use_cub) {
+        unsigned long long* cnt; CK(cudaMalloc(&cnt, 8)); CK(cudaMemset(cnt, 0, 8));
+        diff<<<148 * 8, 256>>>(k, ck, n, cnt);
+        if (pairs) diff<<<148 * 8, 256>>>(v, cv, n, cnt);
+        unsigned long long h; CK(cudaMemcpy(&h, cnt, 8, cudaMemcpyDeviceToHost));
+        printf(" | cub %.3f ms %.2f Gkeys/s | mismatches vs cub: %llu", cub_ms, n / cub_ms / 1e6, h);
+        printf("\n");
+        return h != 0;
+    }
+    printf("\n");
+    return 0;
+}

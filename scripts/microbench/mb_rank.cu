@@ -1,0 +1,84 @@
+// Microbenchmarks that size the ranking primitives on B200 (sm_100a): cycles per warp-level op.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#define ITERS 256
+__device__ __forceinline__ uint32_t hash(uint32_t x) { x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16; return x; }
+
+template <int MODE>
+__global__ void __launch_bounds__(512) k(uint32_t* out, int distinct_mask)
+{
+    __shared__ uint32_t s[16 * 256 + 32 * 256];
+    for (int i = threadIdx.x; i < 16 * 256 + 32 * 256; i += blockDim.x) s[i] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t x = hash(threadIdx.x + blockIdx.x * blockDim.x + 1);
+    uint32_t acc = 0;
+    uint32_t* my = s + warp * 256;
+    const uint32_t lt = (1u << lane) - 1;
+#pragma unroll 4
+    for (int it = 0; it < ITERS; ++it) {
+        x = x * 1664525u + 1013904223u;
+        uint32_t d = (x >> 24) & distinct_mask;
+        if (MODE == 0) { // hardware match.any
+            acc += __popc(__match_any_sync(0xffffffffu, d) & lt);
+        } else if (MODE == 1) { // ballot loop
+            uint32_t peers = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { bool p = (d >> b) & 1; uint32_t m = __ballot_sync(0xffffffffu, p); peers &= p ? m : ~m; }
+            acc += __popc(peers & lt);
+        } else if (MODE == 2) { // smem atomic no return, warp-private 256 bins
+            atomicAdd(&my[d], 1u);
+        } else if (MODE == 3) { // smem atomic with return
+            acc += atomicAdd(&my[d], 1u);
+        } else if (MODE == 4) { // smem atomic, conflict-free layout digit*32+lane (block-shared)
+            atomicAdd(&s[16 * 256 + d * 32 + lane], 1u);
+        } else if (MODE == 5) { // plain LDS random + STS leader
+            uint32_t c = my[d]; acc += c; __syncwarp(); if ((x & 3) == 0) my[d] = c + 1; __syncwarp();
+        } else if (MODE == 6) { // LDS random only
+            acc += my[d];
+        } else if (MODE == 7) { // empty loop baseline
+            acc += d;
+        } else if (MODE == 8) { // atomicOr match-mask (reference's scheme)
+            atomicOr(&my[d], 1u << lane); __syncwarp(); uint32_t m = my[d]; acc += __popc(m & lt); __syncwarp(); if ((m & lt) == 0) my[d] = 0; __syncwarp();
+        }
+    }
+    if (acc == 0x12345678u) out[0] = acc + s[threadIdx.x];
+    if (MODE >= 2 && MODE <= 4 && threadIdx.x == 0 && blockIdx.x == 0) out[1] = s[5];
+}
+
+template <int MODE>
+void run(const char* name, int mask, uint32_t* out)
+{
+    int blocks = 148 * 2;
+    k<MODE><<<blocks, 512>>>(out, mask);
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a);
+    for (int r = 0; r < 10; ++r) k<MODE><<<blocks, 512>>>(out, mask);
+    cudaEventRecord(b); cudaEventSynchronize(b);
+    float ms; cudaEventElapsedTime(&ms, a, b); ms /= 10;
+    double warp_ops = (double)blocks * 16 * ITERS;
+    // per SM: warp_ops/148 ops in ms; report ns per warp-op per SM and cycles at 1.9 GHz
+    double ns = ms * 1e6 / (warp_ops / 148);
+    printf("%-38s mask=0x%02x  %.3f ms  %.2f ns/warp-op/SM  (~%.1f cyc @1.9GHz)\n", name, mask, ms, ns, ns * 1.9);
+}
+
+int main()
+{
+    uint32_t* out; cudaMalloc(&out, 64);
+    for (int mask : {0xff, 0x07, 0x00}) {
+        run<7>("baseline loop", mask, out);
+        run<0>("match.any hw", mask, out);
+        run<1>("ballot-loop match", mask, out);
+        run<2>("ATOMS add noret warp-private", mask, out);
+        run<3>("ATOMS add ret warp-private", mask, out);
+        run<4>("ATOMS add noret digit*32+lane", mask, out);
+        run<5>("LDS+STS(leader) counters", mask, out);
+        run<6>("LDS random", mask, out);
+        run<8>("atomicOr match-mask scheme", mask, out);
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    printf("%s\n", cudaGetErrorString(e));
+    return e != cudaSuccess;
+}
