@@ -166,6 +166,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
         cudaError_t e = cudaGetDevice(&dev);
         if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, dev);
         for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[v]();
+        if (e == cudaSuccess) e = s->table->prepare_histogram();
         s->prepared_err = e;
     });
     if (s->prepared_err != cudaSuccess) {
@@ -204,10 +205,10 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     CUDA_TRY(mark(), "profile event");
 
     {
-        const uint64_t vec_per_block = (uint64_t)HIST_THREADS * 2;
+        const uint64_t vec_per_block = (uint64_t)HIST_THREADS * 4;
         const uint64_t nvec = (uint64_t)n * s->kbytes / 16;
         uint64_t grid = div_up(nvec > 0 ? nvec : 1, vec_per_block);
-        const uint64_t cap = (uint64_t)s->sm_count * 4; // 4 x 512 threads resident per SM
+        const uint64_t cap = (uint64_t)s->sm_count; // one 1024-thread block (128 KiB table) per SM
         if (grid > cap) grid = cap;
         CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bits, passes, sc, (int)grid, stream),
                  "histogram_kernel launch");

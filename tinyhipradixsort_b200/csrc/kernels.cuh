@@ -99,31 +99,56 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_
 // prefixSumExclusiveInplace (kernel.cu:136-204).
 //   hist[p][d]    += #keys whose digit at bit (start_bit + 8p) is d
 //   base[p][0][d]  = exclusive scan over d of hist[p][*]   (written by the last block)
+//
+// One 1024-thread block per SM.  The block-private table is replicated per lane:
+// cell(p, d, lane % REP) with REP = 32 (4-byte keys) or 16 (8-byte keys), 128 KiB either
+// way, so the bank of a shared-memory atomic is the lane id and random digits never
+// bank-conflict (measured on B200: a conflict-free ATOMS costs ~1 cycle/warp, a random
+// one ~4).  Cells are folded over the lanes once at the end.
 // ---------------------------------------------------------------------------------------
-constexpr int HIST_THREADS = 512;
+constexpr int HIST_THREADS = 1024;
+template <int KBYTES> struct HistShape {
+    static constexpr int REP = KBYTES == 4 ? 32 : 16;
+    static constexpr int MAXP = KBYTES;                        // key bits / 8
+    static constexpr size_t BYTES = (size_t)MAXP * RADIX * REP * 4; // 128 KiB
+};
 
 template <class KeyT, int KIND, bool DESC>
-__global__ void __launch_bounds__(HIST_THREADS)
+__global__ void __launch_bounds__(HIST_THREADS, 1)
 histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc)
 {
-    constexpr int KEY_BITS = sizeof(KeyT) * 8;
+    using HS = HistShape<(int)sizeof(KeyT)>;
+    constexpr int REP = HS::REP;
     constexpr int VEC = 16 / sizeof(KeyT);
-    __shared__ uint32_t s_hist[MAX_PASSES * RADIX];
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* tab = reinterpret_cast<uint32_t*>(smem_raw); // [passes][256][REP]
     __shared__ uint32_t s_scan[8];
     __shared__ uint32_t s_last;
 
-    for (int i = threadIdx.x; i < passes * RADIX; i += HIST_THREADS) s_hist[i] = 0;
+    {
+        uint4* z = reinterpret_cast<uint4*>(tab);
+        const int nz = passes * RADIX * REP / 4;
+        for (int i = threadIdx.x; i < nz; i += HIST_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
     __syncthreads();
 
+    uint32_t* my = tab + (threadIdx.x & (REP - 1));
     auto count_key = [&](KeyT raw) {
         auto kb = (sizeof(KeyT) == 4) ? (uint64_t)key_bits32<KIND, DESC>((uint32_t)raw)
                                       : key_bits64<KIND, DESC>((uint64_t)raw);
 #pragma unroll
-        for (int p = 0; p < MAX_PASSES; ++p) {
-            if (p < passes && (int)(start_bit + 8 * p) < KEY_BITS) {
+        for (int p = 0; p < HS::MAXP; ++p) {
+            if (p < passes) {
                 uint32_t d = (uint32_t)(kb >> (start_bit + 8 * p)) & 0xFFu;
-                atomicAdd(&s_hist[p * RADIX + d], 1u);
+                atomicAdd(&my[(p * RADIX + d) * REP], 1u);
             }
+        }
+    };
+    auto count_vec = [&](uint4 a) {
+        if (sizeof(KeyT) == 4) {
+            count_key((KeyT)a.x); count_key((KeyT)a.y); count_key((KeyT)a.z); count_key((KeyT)a.w);
+        } else {
+            count_key((KeyT)(((uint64_t)a.y << 32) | a.x)); count_key((KeyT)(((uint64_t)a.w << 32) | a.z));
         }
     };
 
@@ -133,7 +158,6 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     if (head > n) head = n;
     const uint32_t nvec = (n - head) / VEC;
     const uint32_t tail_begin = head + nvec * VEC;
-
     if (blockIdx.x == 0) {
         if (threadIdx.x < head) count_key(keys[threadIdx.x]);
         if (tail_begin + threadIdx.x < n) count_key(keys[tail_begin + threadIdx.x]);
@@ -141,32 +165,24 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     const uint4* vkeys = reinterpret_cast<const uint4*>(keys + head);
     const uint32_t stride = gridDim.x * HIST_THREADS;
     uint32_t v = blockIdx.x * HIST_THREADS + threadIdx.x;
-    // two independent 128-bit loads in flight per thread
-    for (; v + stride < nvec; v += 2 * stride) {
+    // four independent 128-bit loads in flight per thread (64 KiB per SM)
+    for (; (uint64_t)v + 3ull * stride < nvec; v += 4 * stride) {
         uint4 a = __ldg(vkeys + v);
         uint4 b = __ldg(vkeys + v + stride);
-        if (sizeof(KeyT) == 4) {
-            count_key((KeyT)a.x); count_key((KeyT)a.y); count_key((KeyT)a.z); count_key((KeyT)a.w);
-            count_key((KeyT)b.x); count_key((KeyT)b.y); count_key((KeyT)b.z); count_key((KeyT)b.w);
-        } else {
-            count_key((KeyT)(((uint64_t)a.y << 32) | a.x)); count_key((KeyT)(((uint64_t)a.w << 32) | a.z));
-            count_key((KeyT)(((uint64_t)b.y << 32) | b.x)); count_key((KeyT)(((uint64_t)b.w << 32) | b.z));
-        }
+        uint4 c = __ldg(vkeys + v + 2 * stride);
+        uint4 e = __ldg(vkeys + v + 3 * stride);
+        count_vec(a); count_vec(b); count_vec(c); count_vec(e);
     }
-    if (v < nvec) {
-        uint4 a = __ldg(vkeys + v);
-        if (sizeof(KeyT) == 4) {
-            count_key((KeyT)a.x); count_key((KeyT)a.y); count_key((KeyT)a.z); count_key((KeyT)a.w);
-        } else {
-            count_key((KeyT)(((uint64_t)a.y << 32) | a.x)); count_key((KeyT)(((uint64_t)a.w << 32) | a.z));
-        }
-    }
+    for (; v < nvec; v += stride) count_vec(__ldg(vkeys + v));
     __syncthreads();
 
+    // fold the lane replicas (rotated start: conflict-free) and add to the global histogram
     uint32_t* g_hist = sc.hist();
-    for (int i = threadIdx.x; i < passes * RADIX; i += HIST_THREADS) {
-        uint32_t c = s_hist[i];
-        if (c) atomicAdd(&g_hist[i], c);
+    for (int r = threadIdx.x; r < passes * RADIX; r += HIST_THREADS) {
+        uint32_t c = 0;
+#pragma unroll
+        for (int i = 0; i < REP; ++i) c += tab[r * REP + ((i + threadIdx.x) & (REP - 1))];
+        if (c) atomicAdd(&g_hist[r], c);
     }
 
     // last block to finish turns the histograms into exclusive bin bases
@@ -196,130 +212,137 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
 // Tile arrangement is warp-striped: warp w owns items [w*32*ITEMS, (w+1)*32*ITEMS) of the
 // tile and lane l holds items j*32 + l, so every load is a fully coalesced 128/256-byte
 // request and ranking step j sees 32 consecutive items in lane order.
+//
+// Ranking never uses warp votes (measured on B200: an 8-ballot match costs ~25 SM-cycles
+// per warp step, hardware match.any up to ~60; a random shared-memory atomic ~4).  Each
+// warp owns a table tbl[w][256] of {mask, base} words:
+//   phase A  per item: atomicAdd(base, 1)                       -> per-warp digit counts
+//   scan     thread d: counts -> publish tile aggregate (look-back status, early),
+//            base[w][d] = tile-sorted position of warp w's first item with digit d
+//   phase C  per warp step: atomicOr(mask, 1 << lane); the lanes that share a digit read the
+//            same mask, their rank is popc(mask & lower lanes) (order-free: a set union),
+//            the lowest lane advances base by popc(mask) and clears the mask; key and value
+//            go straight to their tile-sorted slot in shared memory
+//   look-back (thread d) over the predecessors' status words, then a coalesced read-out.
 // ---------------------------------------------------------------------------------------
 template <int VBYTES> struct ValueOf { using type = uint32_t; };
 template <> struct ValueOf<8> { using type = uint2; };
 template <> struct ValueOf<16> { using type = uint4; };
 
-template <int A, int B> struct MaxOf { static constexpr int value = A > B ? A : B; };
-
 template <class KeyT, int VBYTES, int THREADS, int ITEMS>
 struct OnesweepSmem {
     static constexpr int WARPS = THREADS / 32;
     static constexpr int TILE = THREADS * ITEMS;
-    static constexpr int ELEM = MaxOf<(int)sizeof(KeyT), VBYTES>::value;
-    static constexpr size_t STAGE_BYTES = (size_t)TILE * ELEM;
-    static constexpr size_t WARP_CNT_BYTES = (size_t)WARPS * RADIX * 4;
-    static constexpr size_t BYTES = STAGE_BYTES + WARP_CNT_BYTES + RADIX * 4 * 2 + 64;
+    static constexpr size_t TBL_BYTES = (size_t)WARPS * RADIX * 8;
+    static constexpr size_t KEY_BYTES = (size_t)TILE * sizeof(KeyT);
+    static constexpr size_t VAL_BYTES = (size_t)TILE * VBYTES;
+    static constexpr size_t OFF_TBL = 0;
+    static constexpr size_t OFF_VAL = OFF_TBL + TBL_BYTES; // 16-byte aligned (uint4 values)
+    static constexpr size_t OFF_KEY = OFF_VAL + VAL_BYTES;
+    static constexpr size_t OFF_BIN = OFF_KEY + KEY_BYTES;
+    static constexpr size_t BYTES = OFF_BIN + RADIX * 4 + 64;
 };
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS)
-onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
-                const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
-                typename ValueOf<VBYTES>::type* __restrict__ vals_out,
-                uint32_t n, uint32_t bit, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
-                const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out)
+template <bool FULL, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
+__device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+                                              const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
+                                              typename ValueOf<VBYTES>::type* __restrict__ vals_out, uint32_t bit,
+                                              uint32_t* __restrict__ status, const uint32_t* __restrict__ base_in,
+                                              uint32_t* __restrict__ base_out, uint32_t tile, bool last_tile,
+                                              size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw)
 {
     using ValT = typename ValueOf<VBYTES>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS>;
     constexpr int WARPS = SM::WARPS;
-    constexpr int TILE = SM::TILE;
     constexpr bool PAIRS = VBYTES > 0;
 
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw);
-    ValT* s_vals = reinterpret_cast<ValT*>(smem_raw);
-    uint32_t* s_warp_cnt = reinterpret_cast<uint32_t*>(smem_raw + SM::STAGE_BYTES); // [WARPS][256]
-    uint32_t* s_bin_start = s_warp_cnt + WARPS * RADIX;                              // [256]
-    uint32_t* s_off = s_bin_start + RADIX;                                           // [256]
-    uint32_t* s_misc = s_off + RADIX;                                                // [16]
+    uint2* tbl = reinterpret_cast<uint2*>(smem_raw + SM::OFF_TBL);      // [WARPS][256] {mask, base}
+    ValT* s_vals = reinterpret_cast<ValT*>(smem_raw + SM::OFF_VAL);     // [TILE] tile-sorted
+    KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw + SM::OFF_KEY);     // [TILE] tile-sorted
+    uint32_t* s_off = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN); // [256] global - local offset
+    uint32_t* s_misc = s_off + RADIX;                                   // [16]
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
+    uint2* tw = tbl + warp * RADIX;
 
-    // ---- tile ticket: tiles are processed in ticket order, so a tile only ever waits on
-    // tiles that already started (no deadlock whatever the block scheduler does)
-    if (tid == 0) s_misc[8] = atomicAdd(ticket, 1u);
-#pragma unroll
-    for (int i = tid; i < WARPS * RADIX; i += THREADS) s_warp_cnt[i] = 0;
-    __syncthreads();
-    const uint32_t tile = s_misc[8];
-    const uint32_t num_tiles = (n + TILE - 1) / TILE;
-    const size_t tile_base = (size_t)tile * TILE;
-    const uint32_t tile_valid = (n - tile_base) < (size_t)TILE ? (uint32_t)(n - tile_base) : (uint32_t)TILE;
-    const bool full = tile_valid == (uint32_t)TILE;
-
-    // ---- load (warp-striped)
+    // ---- load keys (warp-striped, coalesced)
     KeyT key[ITEMS];
-    ValT val[PAIRS ? ITEMS : 1];
-    uint32_t dig[ITEMS];
     const uint32_t my0 = warp * (32 * ITEMS) + lane;
-    if (full) {
-#pragma unroll
-        for (int j = 0; j < ITEMS; ++j) key[j] = keys_in[tile_base + my0 + j * 32];
-        if (PAIRS) {
-#pragma unroll
-            for (int j = 0; j < ITEMS; ++j) val[j] = vals_in[tile_base + my0 + j * 32];
-        }
-#pragma unroll
-        for (int j = 0; j < ITEMS; ++j) dig[j] = digit_of<KIND, DESC>(key[j], bit);
-    } else {
-#pragma unroll
-        for (int j = 0; j < ITEMS; ++j) {
-            uint32_t idx = my0 + j * 32;
-            bool ok = idx < tile_valid;
-            key[j] = ok ? keys_in[tile_base + idx] : KeyT(0);
-            if (PAIRS) {
-                if (ok) val[j] = vals_in[tile_base + idx];
-                else val[j] = ValT();
-            }
-            // padding items rank behind every real item: last bin, largest index
-            dig[j] = ok ? digit_of<KIND, DESC>(key[j], bit) : 255u;
-        }
-    }
-
-    // ---- rank inside the warp: ballot match + warp-private counters (no atomics)
-    uint32_t rank[ITEMS];
-    uint32_t* my_cnt = s_warp_cnt + warp * RADIX;
-    const uint32_t lane_lt = (1u << lane) - 1u;
+    const KeyT* kin = keys_in + tile_base + my0;
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
-        const uint32_t d = dig[j];
-        uint32_t peers = 0xffffffffu;
+        if (FULL || my0 + j * 32 < tile_valid) key[j] = kin[j * 32];
+        else key[j] = KeyT(0);
+    }
+
+    // ---- phase A: per-warp digit counts
 #pragma unroll
-        for (int b = 0; b < 8; ++b) {
-            const bool p = (d >> b) & 1u;
-            const uint32_t m = __ballot_sync(0xffffffffu, p);
-            peers &= p ? m : ~m;
+    for (int j = 0; j < ITEMS; ++j) {
+        if (FULL || my0 + j * 32 < tile_valid) atomicAdd(&tw[digit_of<KIND, DESC>(key[j], bit)].y, 1u);
+    }
+
+    // values are requested now; their latency hides behind the scan
+    ValT val[PAIRS ? ITEMS : 1];
+    if (PAIRS) {
+        const ValT* vin = vals_in + tile_base + my0;
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            if (FULL || my0 + j * 32 < tile_valid) val[j] = vin[j * 32];
+            else val[j] = ValT();
         }
-        const uint32_t before = my_cnt[d];
-        const uint32_t lower = __popc(peers & lane_lt);
-        rank[j] = before + lower;
-        __syncwarp();
-        if (lower == 0) my_cnt[d] = before + __popc(peers);
-        __syncwarp();
     }
     __syncthreads();
 
-    // ---- per digit: exclusive scan over warps, tile count, publish, look back
-    uint32_t count = 0;
-    if (tid < RADIX) {
+    // ---- scan: thread d owns digit d
+    uint32_t count = 0, bin_start;
+    uint32_t* my_status = status + (size_t)tile * RADIX + tid;
+    {
+        uint32_t c[WARPS];
+        if (tid < RADIX) {
 #pragma unroll
-        for (int w = 0; w < WARPS; ++w) {
-            uint32_t c = s_warp_cnt[w * RADIX + tid];
-            s_warp_cnt[w * RADIX + tid] = count;
-            count += c;
+            for (int w = 0; w < WARPS; ++w) {
+                c[w] = tbl[w * RADIX + tid].y;
+                count += c[w];
+            }
+            // early publication: successors can start summing while this tile still ranks
+            st_relaxed(my_status, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+        }
+        bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
+        if (tid < RADIX) {
+            uint32_t run = bin_start;
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) {
+                tbl[w * RADIX + tid].y = run;
+                run += c[w];
+            }
         }
     }
-    uint32_t published = count;
-    if (tid == RADIX - 1) published -= (uint32_t)TILE - tile_valid;
-    uint32_t* my_status = status + (size_t)tile * RADIX + tid;
-    if (tid < RADIX) st_relaxed(my_status, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | published);
+    __syncthreads();
 
-    const uint32_t bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
+    // ---- phase C: rank inside the warp step and stage at the tile-sorted position
+    const uint32_t lane_bit = 1u << lane;
+    const uint32_t lane_lt = lane_bit - 1u;
+#pragma unroll
+    for (int j = 0; j < ITEMS; ++j) {
+        const bool ok = FULL || my0 + j * 32 < tile_valid;
+        const uint32_t d = digit_of<KIND, DESC>(key[j], bit);
+        if (ok) atomicOr(&tw[d].x, lane_bit);
+        __syncwarp();
+        uint2 e = make_uint2(0u, 0u);
+        if (ok) e = tw[d];
+        const uint32_t lower = __popc(e.x & lane_lt);
+        __syncwarp();
+        if (ok && lower == 0) tw[d] = make_uint2(0u, e.y + __popc(e.x));
+        __syncwarp();
+        if (ok) {
+            s_keys[e.y + lower] = key[j];
+            if (PAIRS) s_vals[e.y + lower] = val[j];
+        }
+    }
 
+    // ---- decoupled look-back (thread d), then the global - local offset of every bin
     if (tid < RADIX) {
         uint32_t excl = 0;
         if (tile != 0) {
@@ -331,43 +354,60 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 if ((s >> FLAG_SHIFT) == 2u) break;
                 look -= RADIX;
             }
-            st_relaxed(my_status, FLAG_PREFIX | (excl + published));
+            st_relaxed(my_status, FLAG_PREFIX | (excl + count));
         }
         const uint32_t gbase = base_in[tid] + excl;
-        s_bin_start[tid] = bin_start;
         s_off[tid] = gbase - bin_start;
-        if (base_out != nullptr && tile == num_tiles - 1) base_out[tid] = gbase + published;
+        if (base_out != nullptr && last_tile) base_out[tid] = gbase + count;
     }
     __syncthreads();
 
-    // ---- stage keys in tile-sorted order, then stream them out in runs
-    uint32_t pos[ITEMS];
-#pragma unroll
-    for (int j = 0; j < ITEMS; ++j) {
-        pos[j] = s_bin_start[dig[j]] + my_cnt[dig[j]] + rank[j];
-        s_keys[pos[j]] = key[j];
-    }
-    __syncthreads();
-    uint32_t dst[ITEMS];
+    // ---- read-out: consecutive threads take consecutive tile-sorted slots -> coalesced runs
 #pragma unroll
     for (int k = 0; k < ITEMS; ++k) {
         const uint32_t p = k * THREADS + tid;
-        const KeyT kk = s_keys[p];
-        const uint32_t d = digit_of<KIND, DESC>(kk, bit);
-        dst[k] = s_off[d] + p;
-        if (full || p < tile_valid) keys_out[dst[k]] = kk;
-    }
-    if (PAIRS) {
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < ITEMS; ++j) s_vals[pos[j]] = val[j];
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < ITEMS; ++k) {
-            const uint32_t p = k * THREADS + tid;
-            if (full || p < tile_valid) vals_out[dst[k]] = s_vals[p];
+        if (FULL || p < tile_valid) {
+            const KeyT kk = s_keys[p];
+            const uint32_t dst = s_off[digit_of<KIND, DESC>(kk, bit)] + p;
+            keys_out[dst] = kk;
+            if (PAIRS) vals_out[dst] = s_vals[p];
         }
     }
+}
+
+template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+                const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
+                typename ValueOf<VBYTES>::type* __restrict__ vals_out,
+                uint32_t n, uint32_t bit, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
+                const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out)
+{
+    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS>;
+    constexpr int TILE = SM::TILE;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* s_misc = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN) + RADIX;
+
+    // ---- tile ticket: tiles are processed in ticket order, so a tile only ever waits on
+    // tiles that already started (no deadlock whatever the block scheduler does)
+    if (threadIdx.x == 0) s_misc[15] = atomicAdd(ticket, 1u);
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
+        for (int i = threadIdx.x; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
+    const uint32_t tile = s_misc[15];
+    const uint32_t num_tiles = (n + TILE - 1) / TILE;
+    const size_t tile_base = (size_t)tile * TILE;
+    const uint32_t tile_valid = (n - tile_base) < (size_t)TILE ? (uint32_t)(n - tile_base) : (uint32_t)TILE;
+    if (tile_valid == (uint32_t)TILE)
+        onesweep_tile<true, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(keys_in, keys_out, vals_in, vals_out, bit, status,
+                                                                      base_in, base_out, tile, tile == num_tiles - 1,
+                                                                      tile_base, tile_valid, smem_raw);
+    else
+        onesweep_tile<false, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(keys_in, keys_out, vals_in, vals_out, bit, status,
+                                                                       base_in, base_out, tile, tile == num_tiles - 1,
+                                                                       tile_base, tile_valid, smem_raw);
 }
 
 } // namespace thrs_b200

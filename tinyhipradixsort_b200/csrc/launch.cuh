@@ -7,14 +7,15 @@
 
 namespace thrs_b200 {
 
-// Tile shape per (key bytes, value bytes).  THREADS x ITEMS items per tile.
-template <int KBYTES, int VBYTES> struct Tuning { static constexpr int THREADS = 512, ITEMS = 16; };
-template <> struct Tuning<4, 8> { static constexpr int THREADS = 512, ITEMS = 12; };
-template <> struct Tuning<4, 16> { static constexpr int THREADS = 512, ITEMS = 8; };
-template <> struct Tuning<8, 0> { static constexpr int THREADS = 512, ITEMS = 12; };
-template <> struct Tuning<8, 4> { static constexpr int THREADS = 512, ITEMS = 12; };
-template <> struct Tuning<8, 8> { static constexpr int THREADS = 512, ITEMS = 12; };
-template <> struct Tuning<8, 16> { static constexpr int THREADS = 512, ITEMS = 8; };
+// Tile shape per (key bytes, value bytes).  THREADS x ITEMS items per tile; MINB = resident
+// blocks per SM the register allocation is bounded for.
+template <int KBYTES, int VBYTES> struct Tuning { static constexpr int THREADS = 512, ITEMS = 16, MINB = 2; };
+template <> struct Tuning<4, 8> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
+template <> struct Tuning<4, 16> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
+template <> struct Tuning<8, 0> { static constexpr int THREADS = 512, ITEMS = 12, MINB = 2; };
+template <> struct Tuning<8, 4> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
+template <> struct Tuning<8, 8> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
+template <> struct Tuning<8, 16> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
 
 struct OnesweepArgs {
     const void* keys_in;
@@ -35,6 +36,7 @@ struct KernelTable {
                              cudaStream_t stream);
     cudaError_t (*onesweep[4])(const OnesweepArgs& a, cudaStream_t stream);
     cudaError_t (*prepare[4])(); // opt in to > 48 KiB dynamic shared memory
+    cudaError_t (*prepare_histogram)();
     uint32_t tile_items[4];
 };
 
@@ -42,9 +44,16 @@ template <class KeyT, int KIND, bool DESC>
 cudaError_t launch_histogram(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
                              cudaStream_t stream)
 {
-    histogram_kernel<KeyT, KIND, DESC>
-        <<<grid, HIST_THREADS, 0, stream>>>(static_cast<const KeyT*>(keys), n, start_bit, passes, sc);
+    histogram_kernel<KeyT, KIND, DESC><<<grid, HIST_THREADS, HistShape<(int)sizeof(KeyT)>::BYTES, stream>>>(
+        static_cast<const KeyT*>(keys), n, start_bit, passes, sc);
     return cudaGetLastError();
+}
+
+template <class KeyT, int KIND, bool DESC>
+cudaError_t prepare_histogram()
+{
+    return cudaFuncSetAttribute(histogram_kernel<KeyT, KIND, DESC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)HistShape<(int)sizeof(KeyT)>::BYTES);
 }
 
 template <class KeyT, int KIND, bool DESC, int VBYTES>
@@ -54,7 +63,7 @@ cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS>;
     using ValT = typename ValueOf<VBYTES>::type;
     const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
-    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS><<<tiles, T::THREADS, SM::BYTES, stream>>>(
+    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB><<<tiles, T::THREADS, SM::BYTES, stream>>>(
         static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
         static_cast<ValT*>(a.vals_out), a.n, a.bit, a.status, a.ticket, a.base_in, a.base_out);
     return cudaGetLastError();
@@ -65,7 +74,7 @@ cudaError_t prepare_onesweep()
 {
     using T = Tuning<(int)sizeof(KeyT), VBYTES>;
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS>;
-    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS>,
+    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES);
 }
 
@@ -78,6 +87,7 @@ const KernelTable* make_table()
          &launch_onesweep<KeyT, KIND, DESC, 8>, &launch_onesweep<KeyT, KIND, DESC, 16>},
         {&prepare_onesweep<KeyT, KIND, DESC, 0>, &prepare_onesweep<KeyT, KIND, DESC, 4>,
          &prepare_onesweep<KeyT, KIND, DESC, 8>, &prepare_onesweep<KeyT, KIND, DESC, 16>},
+        &prepare_histogram<KeyT, KIND, DESC>,
         {(uint32_t)(Tuning<(int)sizeof(KeyT), 0>::THREADS * Tuning<(int)sizeof(KeyT), 0>::ITEMS),
          (uint32_t)(Tuning<(int)sizeof(KeyT), 4>::THREADS * Tuning<(int)sizeof(KeyT), 4>::ITEMS),
          (uint32_t)(Tuning<(int)sizeof(KeyT), 8>::THREADS * Tuning<(int)sizeof(KeyT), 8>::ITEMS),
