@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <dlfcn.h>
 #include "../include/thrs_b200.h"
 
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); exit(1); } } while (0)
@@ -91,6 +92,16 @@ int main(int argc, char** argv)
         if (r >= 2 && p.total_ms < best.total_ms) best = p;
     }
     CK(cudaDeviceSynchronize());
+    if (void* f = dlsym(RTLD_DEFAULT, "thrs_dev_phase")) { // dev-only variant built with -DTHRS_PHASE_TIMING
+        unsigned long long ph[16];
+        ((void (*)(unsigned long long*, int))f)(ph, 1);
+        unsigned long long tot = 0;
+        for (int i = 0; i < 8; ++i) tot += ph[i];
+        const char* names[8] = {"load", "phaseA", "bar1", "scan+bar2", "phaseC", "lookback", "bar3", "readout"};
+        printf("phase share of warp-0 cycles:");
+        for (int i = 0; i < 8; ++i) printf(" %s %.1f%%", names[i], 100.0 * ph[i] / tot);
+        printf("\n");
+    }
     int passes = (eb - sb) / 8;
     double bytes = (double)n * 4 + (double)passes * 2 * n * (pairs ? 8 : 4);
     printf("n=%u pairs=%d dist=%s bits[%d,%d): thrs %.3f ms (memset %.3f hist %.3f passes", n, pairs, dname, sb, eb,

@@ -40,12 +40,51 @@ __global__ void __launch_bounds__(512) k(uint32_t* out, int distinct_mask)
             acc += my[d];
         } else if (MODE == 7) { // empty loop baseline
             acc += d;
+        } else if (MODE == 9) { // ballot match + LDS/STS leader counters (does VOTE overlap the smem pipe?)
+            uint32_t peers = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { bool p = (d >> b) & 1; uint32_t m = __ballot_sync(0xffffffffu, p); peers &= p ? m : ~m; }
+            uint32_t c = my[d]; uint32_t lower = __popc(peers & lt); acc += c + lower; __syncwarp(); if (lower == 0) my[d] = c + __popc(peers); __syncwarp();
+        } else if (MODE == 10) { // 6 shuffles
+            uint32_t v = d;
+#pragma unroll
+            for (int b = 0; b < 6; ++b) v += __shfl_xor_sync(0xffffffffu, v, 1 << (b % 5));
+            acc += v;
+        } else if (MODE == 11) { // 2 random ATOMS + 2 random LDS (is an ATOMS wavefront 2 pipe cycles?)
+            atomicAdd(&my[d], 1u); atomicOr(&my[(d * 7 + 3) & 255], 1u << lane); acc += my[(d + 17) & 255]; acc += my[(d * 5 + 1) & 255];
+        } else if (MODE == 12) { // 4 random LDS
+            acc += my[d]; acc += my[(d * 7 + 3) & 255]; acc += my[(d + 17) & 255]; acc += my[(d * 5 + 1) & 255];
+        } else if (MODE == 13) { // 4 random ATOMS
+            atomicAdd(&my[d], 1u); atomicOr(&my[(d * 7 + 3) & 255], 1u << lane); atomicAdd(&my[(d + 17) & 255], 1u); atomicAdd(&my[(d * 5 + 1) & 255], 1u);
+        } else if (MODE == 14) { // ballot match + 4 random LDS
+            uint32_t peers = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { bool p = (d >> b) & 1; uint32_t m = __ballot_sync(0xffffffffu, p); peers &= p ? m : ~m; }
+            acc += __popc(peers & lt);
+            acc += my[d]; acc += my[(d * 7 + 3) & 255]; acc += my[(d + 17) & 255]; acc += my[(d * 5 + 1) & 255];
+        } else if (MODE == 15) { // 4 random STS
+            my[d] = x; my[(d * 7 + 3) & 255] = x; my[(d + 17) & 255] = x; my[(d * 5 + 1) & 255] = x;
+        } else if (MODE == 16) { // 4 random STS.64
+            uint2* m2 = (uint2*)s + warp * 256;
+            m2[d] = make_uint2(x, x); m2[(d * 7 + 3) & 255] = make_uint2(x, x); m2[(d + 17) & 255] = make_uint2(x, x); m2[(d * 5 + 1) & 255] = make_uint2(x, x);
+        } else if (MODE == 17) { // 4 random LDS.64
+            uint2* m2 = (uint2*)s + warp * 256;
+            uint2 a = m2[d], b = m2[(d * 7 + 3) & 255], c = m2[(d + 17) & 255], e = m2[(d * 5 + 1) & 255];
+            acc += a.x + a.y + b.x + b.y + c.x + c.y + e.x + e.y;
+        } else if (MODE == 18) { // 4 conflict-free STS
+            my[lane] = x; my[lane + 32] = x; my[lane + 64] = x; my[lane + 96] = x;
+        } else if (MODE == 19) { // 4 conflict-free LDS
+            acc += my[lane] + my[lane + 32 + (d & 32)] + my[lane + 64 + (d & 64)] + my[lane + 128 + (d & 96)];
+        } else if (MODE == 20) { // 4 random STS over 8192 words (staging-like, block shared)
+            uint32_t h = hash(x); s[h & 8191] = x; s[(h >> 8) & 8191] = x; s[(h >> 16) & 8191] = x; s[(h >> 19) & 8191] = x;
+        } else if (MODE == 21) { // 4 random LDS over 8192 words
+            uint32_t h = hash(x); acc += s[h & 8191] + s[(h >> 8) & 8191] + s[(h >> 16) & 8191] + s[(h >> 19) & 8191];
         } else if (MODE == 8) { // atomicOr match-mask (reference's scheme)
             atomicOr(&my[d], 1u << lane); __syncwarp(); uint32_t m = my[d]; acc += __popc(m & lt); __syncwarp(); if ((m & lt) == 0) my[d] = 0; __syncwarp();
         }
     }
     if (acc == 0x12345678u) out[0] = acc + s[threadIdx.x];
-    if (MODE >= 2 && MODE <= 4 && threadIdx.x == 0 && blockIdx.x == 0) out[1] = s[5];
+    __syncthreads(); if ((MODE >= 2 && MODE <= 4) || MODE >= 15) { if (blockIdx.x == 0) out[2 + (threadIdx.x & 7)] = s[threadIdx.x * 7] + s[threadIdx.x + 4096]; }
 }
 
 template <int MODE>
@@ -67,7 +106,7 @@ void run(const char* name, int mask, uint32_t* out)
 int main()
 {
     uint32_t* out; cudaMalloc(&out, 64);
-    for (int mask : {0xff, 0x07, 0x00}) {
+    for (int mask : {0xff}) {
         run<7>("baseline loop", mask, out);
         run<0>("match.any hw", mask, out);
         run<1>("ballot-loop match", mask, out);
@@ -77,6 +116,19 @@ int main()
         run<5>("LDS+STS(leader) counters", mask, out);
         run<6>("LDS random", mask, out);
         run<8>("atomicOr match-mask scheme", mask, out);
+        run<15>("4 STS random", mask, out);
+        run<16>("4 STS.64 random", mask, out);
+        run<17>("4 LDS.64 random", mask, out);
+        run<18>("4 STS conflict-free", mask, out);
+        run<19>("4 LDS conflict-free", mask, out);
+        run<20>("4 STS random 8192 words", mask, out);
+        run<21>("4 LDS random 8192 words", mask, out);
+        run<9>("ballot match + LDS/STS counters", mask, out);
+        run<10>("6 x SHFL.XOR", mask, out);
+        run<11>("2 ATOMS + 2 LDS random", mask, out);
+        run<12>("4 LDS random", mask, out);
+        run<13>("4 ATOMS random", mask, out);
+        run<14>("ballot match + 4 LDS random", mask, out);
     }
     cudaError_t e = cudaDeviceSynchronize();
     printf("%s\n", cudaGetErrorString(e));

@@ -133,7 +133,7 @@ int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out)
     const uint32_t t_pairs = s->table->tile_items[s->vslot];
     const uint64_t tiles = div_up(n, t_keys < t_pairs ? t_keys : t_pairs);
     const uint64_t passes = (uint64_t)s->kbytes; // key bits / 8
-    out->pSumBuffer = align16(4ull * (Scratch::CONTROL_WORDS + passes * tiles * RADIX));
+    out->pSumBuffer = align16(4ull * (Scratch::CONTROL_WORDS + passes * Scratch::pass_words(tiles)));
     out->keyOutBuffer = align16((uint64_t)s->kbytes * n);
     out->valueOutBuffer = align16((uint64_t)s->vbytes * n);
     return THRS_OK;
@@ -200,7 +200,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     CUDA_TRY(mark(), "profile event");
 
     // zero: histograms, bases, tickets, counters and the status rows of the passes we run
-    const size_t clear_bytes = 4ull * (Scratch::CONTROL_WORDS + (uint64_t)passes * tiles_total * RADIX);
+    const size_t clear_bytes = 4ull * (Scratch::CONTROL_WORDS + (uint64_t)passes * Scratch::pass_words(tiles_total));
     CUDA_TRY(cudaMemsetAsync(temp, 0, clear_bytes, stream), "cudaMemsetAsync(scratch)");
     CUDA_TRY(mark(), "profile event");
 
@@ -232,6 +232,10 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
             a.n = (uint32_t)count;
             a.bit = (uint32_t)(start_bits + 8 * p);
             a.status = sc.status(p, tiles_total) + (first / tile) * RADIX;
+            // a part's groups never share a row with the previous part's (first/tile/16 + q)
+            const uint64_t group0 = first / tile / GROUP_TILES + (uint64_t)q;
+            a.gsum = sc.gsum(p, tiles_total) + group0 * RADIX;
+            a.gprefix = sc.gprefix(p, tiles_total) + group0 * RADIX;
             a.ticket = sc.ticket(p, q);
             a.base_in = sc.base(p, q);
             a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;

@@ -6,3 +6,15 @@ const KernelTable* table_u32(bool desc)
     return desc ? make_table<uint32_t, 0, true>() : make_table<uint32_t, 0, false>();
 }
 } // namespace thrs_b200
+
+#ifdef THRS_PHASE_TIMING
+extern "C" __attribute__((visibility("default"))) void thrs_dev_phase(unsigned long long* out, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, thrs_b200::g_phase, sizeof(unsigned long long) * 16);
+    if (reset) {
+        unsigned long long z[16] = {};
+        cudaMemcpyToSymbol(thrs_b200::g_phase, z, sizeof(z));
+    }
+}
+#endif

@@ -27,6 +27,14 @@ constexpr uint32_t FLAG_SHIFT = 30;
 constexpr uint32_t FLAG_AGGREGATE = 1u << FLAG_SHIFT; // tile-local count published
 constexpr uint32_t FLAG_PREFIX = 2u << FLAG_SHIFT;    // inclusive prefix over tiles 0..t published
 constexpr uint32_t VALUE_MASK = (1u << FLAG_SHIFT) - 1u;
+// Two-level look-back: tiles are grouped GROUP_TILES at a time.  Every tile adds its digit
+// counts into its group's accumulator row with one atomic per digit whose upper bits count the
+// arrivals: word = (tiles arrived << GROUP_SUM_BITS) | sum of their counts, so "group complete"
+// needs no second flag and no fence.  gprefix[g] = inclusive prefix through group g-1.
+constexpr int GROUP_TILES = 16; // Scratch::groups_of assumes 16
+constexpr uint32_t GROUP_SUM_BITS = 26;
+constexpr uint32_t GROUP_SUM_MASK = (1u << GROUP_SUM_BITS) - 1u;
+constexpr int GROUP_LOOK = 4; // groups examined per round
 
 // Scratch ("pSumBuffer") layout in u32 words.  Fixed-size control block first, then the
 // look-back status rows of every pass: status[pass][tile][256].
@@ -48,11 +56,42 @@ struct Scratch {
         return p + HIST_WORDS + BASE_WORDS + (size_t)pass * MAX_PARTS + part;
     }
     __host__ __device__ uint32_t* misc() const { return p + HIST_WORDS + BASE_WORDS + TICKET_WORDS; }
+    // per pass: status[tiles][256] | group accumulators[groups][256] | group prefixes[groups][256]
+    static __host__ __device__ size_t groups_of(size_t tiles_total) { return tiles_total / 16 + MAX_PARTS + 1; }
+    static __host__ __device__ size_t pass_words(size_t tiles_total)
+    {
+        return (tiles_total + 2 * groups_of(tiles_total)) * RADIX;
+    }
     __host__ __device__ uint32_t* status(int pass, size_t tiles_total) const
     {
-        return p + CONTROL_WORDS + (size_t)pass * tiles_total * RADIX;
+        return p + CONTROL_WORDS + (size_t)pass * pass_words(tiles_total);
+    }
+    __host__ __device__ uint32_t* gsum(int pass, size_t tiles_total) const
+    {
+        return status(pass, tiles_total) + tiles_total * RADIX;
+    }
+    __host__ __device__ uint32_t* gprefix(int pass, size_t tiles_total) const
+    {
+        return gsum(pass, tiles_total) + groups_of(tiles_total) * RADIX;
     }
 };
+
+#ifdef THRS_PHASE_TIMING
+// dev-only: per-phase clock accounting of warp 0 of every tile (scripts/devbench prints it)
+static __device__ unsigned long long g_phase[16];
+#define PHASE_MARK(i)                                                        \
+    do {                                                                     \
+        if (threadIdx.x == 0) {                                              \
+            long long now__ = clock64();                                     \
+            atomicAdd(&g_phase[i], (unsigned long long)(now__ - phase_t0));  \
+            phase_t0 = now__;                                                \
+        }                                                                    \
+    } while (0)
+#define PHASE_BEGIN() long long phase_t0 = clock64()
+#else
+#define PHASE_MARK(i) do { } while (0)
+#define PHASE_BEGIN() do { } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p)
 {
@@ -225,6 +264,13 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
 //            go straight to their tile-sorted slot in shared memory
 //   look-back (thread d) over the predecessors' status words, then a coalesced read-out.
 // ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t val32(uint32_t v) { return v; }
+__device__ __forceinline__ uint32_t val32(uint2 v) { return v.x; } // never used: PACKED implies 4-byte values
+__device__ __forceinline__ uint32_t val32(uint4 v) { return v.x; }
+__device__ __forceinline__ void store32(uint32_t* p, uint32_t v) { *p = v; }
+__device__ __forceinline__ void store32(uint2*, uint32_t) {}
+__device__ __forceinline__ void store32(uint4*, uint32_t) {}
+
 template <int VBYTES> struct ValueOf { using type = uint32_t; };
 template <> struct ValueOf<8> { using type = uint2; };
 template <> struct ValueOf<16> { using type = uint4; };
@@ -247,7 +293,8 @@ template <bool FULL, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, i
 __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                                               const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
                                               typename ValueOf<VBYTES>::type* __restrict__ vals_out, uint32_t bit,
-                                              uint32_t* __restrict__ status, const uint32_t* __restrict__ base_in,
+                                              uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
+                                              uint32_t* __restrict__ gprefix, const uint32_t* __restrict__ base_in,
                                               uint32_t* __restrict__ base_out, uint32_t tile, bool last_tile,
                                               size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw)
 {
@@ -255,8 +302,12 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS>;
     constexpr int WARPS = SM::WARPS;
     constexpr bool PAIRS = VBYTES > 0;
+    // 4-byte key + 4-byte value travel through shared memory as one 8-byte element: a random
+    // 64-bit store costs ~5.2 wavefronts per warp against 2 x 3.9 for two 32-bit ones
+    constexpr bool PACKED = sizeof(KeyT) == 4 && VBYTES == 4;
 
     uint2* tbl = reinterpret_cast<uint2*>(smem_raw + SM::OFF_TBL);      // [WARPS][256] {mask, base}
+    uint2* s_kv = reinterpret_cast<uint2*>(smem_raw + SM::OFF_VAL);     // [TILE] {key, value} when PACKED
     ValT* s_vals = reinterpret_cast<ValT*>(smem_raw + SM::OFF_VAL);     // [TILE] tile-sorted
     KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw + SM::OFF_KEY);     // [TILE] tile-sorted
     uint32_t* s_off = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN); // [256] global - local offset
@@ -267,6 +318,7 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
     const int warp = tid >> 5;
     uint2* tw = tbl + warp * RADIX;
 
+    PHASE_BEGIN();
     // ---- load keys (warp-striped, coalesced)
     KeyT key[ITEMS];
     const uint32_t my0 = warp * (32 * ITEMS) + lane;
@@ -278,6 +330,10 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
     }
 
     // ---- phase A: per-warp digit counts
+#ifdef THRS_PHASE_TIMING
+    if (key[ITEMS - 1] == 0x12345677u && key[0] == 0x7654321u) g_phase[15] = 1; // wait for the loads
+    PHASE_MARK(0);
+#endif
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         if (FULL || my0 + j * 32 < tile_valid) atomicAdd(&tw[digit_of<KIND, DESC>(key[j], bit)].y, 1u);
@@ -293,7 +349,9 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
             else val[j] = ValT();
         }
     }
+    PHASE_MARK(1);
     __syncthreads();
+    PHASE_MARK(2);
 
     // ---- scan: thread d owns digit d
     uint32_t count = 0, bin_start;
@@ -308,6 +366,7 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
             }
             // early publication: successors can start summing while this tile still ranks
             st_relaxed(my_status, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+            atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
         }
         bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
         if (tid < RADIX) {
@@ -320,6 +379,7 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
         }
     }
     __syncthreads();
+    PHASE_MARK(3);
 
     // ---- phase C: rank inside the warp step and stage at the tile-sorted position
     const uint32_t lane_bit = 1u << lane;
@@ -337,22 +397,67 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
         if (ok && lower == 0) tw[d] = make_uint2(0u, e.y + __popc(e.x));
         __syncwarp();
         if (ok) {
-            s_keys[e.y + lower] = key[j];
-            if (PAIRS) s_vals[e.y + lower] = val[j];
+            if (PACKED) s_kv[e.y + lower] = make_uint2((uint32_t)key[j], val32(val[j]));
+            else {
+                s_keys[e.y + lower] = key[j];
+                if (PAIRS) s_vals[e.y + lower] = val[j];
+            }
         }
     }
 
-    // ---- decoupled look-back (thread d), then the global - local offset of every bin
+    PHASE_MARK(4);
+    // ---- decoupled look-back (thread d), then the global - local offset of every bin.
+    // Under load a status read takes ~2.5 us (it queues behind the SM's own bulk traffic) and a
+    // tile finishes every ~55 ns, so ~35 predecessors have no inclusive prefix yet when a tile
+    // looks (measured: a 16-wide serial-window walk took 3 rounds = 45 % of a tile's lifetime).
+    // One round of independent loads here covers the tile's own group (<= 15 rows) plus
+    // GROUP_LOOK complete groups (64 tiles) through their accumulator rows.
     if (tid < RADIX) {
         uint32_t excl = 0;
         if (tile != 0) {
-            const uint32_t* look = my_status - RADIX;
-            while (true) {
-                uint32_t s;
-                do { s = ld_relaxed(look); } while ((s >> FLAG_SHIFT) == 0u);
-                excl += s & VALUE_MASK;
-                if ((s >> FLAG_SHIFT) == 2u) break;
-                look -= RADIX;
+            const uint32_t g = tile / GROUP_TILES, r = tile % GROUP_TILES;
+            const uint32_t* col = status + tid;
+            const uint32_t* gs = gsum + tid;
+            uint32_t* gp = gprefix + tid;
+            uint32_t v[GROUP_TILES - 1], ga[GROUP_LOOK], gq[GROUP_LOOK];
+#pragma unroll
+            for (int i = 0; i < GROUP_TILES - 1; ++i)
+                v[i] = ((uint32_t)i < r) ? ld_relaxed(col + (size_t)(tile - 1 - i) * RADIX) : 0u;
+#pragma unroll
+            for (int j = 0; j < GROUP_LOOK; ++j) {
+                const bool in = g >= (uint32_t)j + 1u; // group g-j has a predecessor group
+                gq[j] = in ? ld_relaxed(gp + (size_t)(g - j) * RADIX) : FLAG_PREFIX; // prefix through group g-j-1
+                ga[j] = in ? ld_relaxed(gs + (size_t)(g - j - 1) * RADIX) : 0u;      // accumulator of group g-j-1
+            }
+            bool done = false;
+#pragma unroll
+            for (int i = 0; i < GROUP_TILES - 1; ++i) {
+                if ((uint32_t)i < r && !done) {
+                    uint32_t sv = v[i];
+                    while ((sv >> FLAG_SHIFT) == 0u) sv = ld_relaxed(col + (size_t)(tile - 1 - i) * RADIX);
+                    excl += sv & VALUE_MASK;
+                    done = (sv >> FLAG_SHIFT) == 2u;
+                }
+            }
+            if (!done) {
+                // excl = counts of the group's earlier tiles; add the prefix through group g-1
+                uint32_t pg = 0, gg = g;
+                bool have = false;
+#pragma unroll
+                for (int j = 0; j < GROUP_LOOK; ++j) {
+                    if (!have && gg == g - (uint32_t)j) {
+                        if ((gq[j] >> FLAG_SHIFT) == 2u) { pg += gq[j] & VALUE_MASK; have = true; }
+                        else if ((ga[j] >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += ga[j] & GROUP_SUM_MASK; --gg; }
+                    }
+                }
+                while (!have) { // beyond the prefetched rows, or a group still filling: poll (all its tiles run)
+                    const uint32_t q = gg == 0u ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
+                    if ((q >> FLAG_SHIFT) == 2u) { pg += q & VALUE_MASK; have = true; break; }
+                    const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
+                    if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
+                }
+                st_relaxed(gp + (size_t)g * RADIX, FLAG_PREFIX | pg); // helps the rest of this group and the next ones
+                excl += pg;
             }
             st_relaxed(my_status, FLAG_PREFIX | (excl + count));
         }
@@ -360,19 +465,29 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
         s_off[tid] = gbase - bin_start;
         if (base_out != nullptr && last_tile) base_out[tid] = gbase + count;
     }
+    PHASE_MARK(5);
     __syncthreads();
+    PHASE_MARK(6);
 
     // ---- read-out: consecutive threads take consecutive tile-sorted slots -> coalesced runs
 #pragma unroll
     for (int k = 0; k < ITEMS; ++k) {
         const uint32_t p = k * THREADS + tid;
         if (FULL || p < tile_valid) {
-            const KeyT kk = s_keys[p];
-            const uint32_t dst = s_off[digit_of<KIND, DESC>(kk, bit)] + p;
-            keys_out[dst] = kk;
-            if (PAIRS) vals_out[dst] = s_vals[p];
+            if (PACKED) {
+                const uint2 kv = s_kv[p];
+                const uint32_t dst = s_off[digit_of<KIND, DESC>((KeyT)kv.x, bit)] + p;
+                keys_out[dst] = (KeyT)kv.x;
+                store32(vals_out + dst, kv.y);
+            } else {
+                const KeyT kk = s_keys[p];
+                const uint32_t dst = s_off[digit_of<KIND, DESC>(kk, bit)] + p;
+                keys_out[dst] = kk;
+                if (PAIRS) vals_out[dst] = s_vals[p];
+            }
         }
     }
+    PHASE_MARK(7);
 }
 
 template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB>
@@ -380,10 +495,12 @@ __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
                 typename ValueOf<VBYTES>::type* __restrict__ vals_out,
-                uint32_t n, uint32_t bit, uint32_t* __restrict__ status, uint32_t* __restrict__ ticket,
+                uint32_t n, uint32_t bit, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
+                uint32_t* __restrict__ gprefix, uint32_t* __restrict__ ticket,
                 const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out)
 {
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS>;
+    static_assert((uint64_t)GROUP_TILES * SM::TILE < (1ull << GROUP_SUM_BITS), "group accumulator overflow");
     constexpr int TILE = SM::TILE;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_misc = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN) + RADIX;
@@ -402,11 +519,11 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     const uint32_t tile_valid = (n - tile_base) < (size_t)TILE ? (uint32_t)(n - tile_base) : (uint32_t)TILE;
     if (tile_valid == (uint32_t)TILE)
         onesweep_tile<true, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(keys_in, keys_out, vals_in, vals_out, bit, status,
-                                                                      base_in, base_out, tile, tile == num_tiles - 1,
+                                                                      gsum, gprefix, base_in, base_out, tile, tile == num_tiles - 1,
                                                                       tile_base, tile_valid, smem_raw);
     else
         onesweep_tile<false, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(keys_in, keys_out, vals_in, vals_out, bit, status,
-                                                                       base_in, base_out, tile, tile == num_tiles - 1,
+                                                                       gsum, gprefix, base_in, base_out, tile, tile == num_tiles - 1,
                                                                        tile_base, tile_valid, smem_raw);
 }
 

@@ -9,7 +9,14 @@ namespace thrs_b200 {
 
 // Tile shape per (key bytes, value bytes).  THREADS x ITEMS items per tile; MINB = resident
 // blocks per SM the register allocation is bounded for.
-template <int KBYTES, int VBYTES> struct Tuning { static constexpr int THREADS = 512, ITEMS = 16, MINB = 2; };
+#ifndef THRS_TUNE_THREADS
+#define THRS_TUNE_THREADS 512
+#define THRS_TUNE_ITEMS 16
+#define THRS_TUNE_MINB 2
+#endif
+template <int KBYTES, int VBYTES> struct Tuning {
+    static constexpr int THREADS = THRS_TUNE_THREADS, ITEMS = THRS_TUNE_ITEMS, MINB = THRS_TUNE_MINB;
+};
 template <> struct Tuning<4, 8> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
 template <> struct Tuning<4, 16> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
 template <> struct Tuning<8, 0> { static constexpr int THREADS = 512, ITEMS = 12, MINB = 2; };
@@ -24,7 +31,9 @@ struct OnesweepArgs {
     void* vals_out;
     uint32_t n;   // items of this part
     uint32_t bit; // first bit of the digit
-    uint32_t* status;
+    uint32_t* status;  // [tiles][256] look-back words of this part
+    uint32_t* gsum;    // [groups][256] group accumulators of this part
+    uint32_t* gprefix; // [groups][256] prefix through the previous group
     uint32_t* ticket;
     const uint32_t* base_in;
     uint32_t* base_out;
@@ -65,7 +74,7 @@ cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
     const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
     onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB><<<tiles, T::THREADS, SM::BYTES, stream>>>(
         static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
-        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.status, a.ticket, a.base_in, a.base_out);
+        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out);
     return cudaGetLastError();
 }
 
