@@ -301,3 +301,14 @@ def test_misaligned_key_pointer_keys_not_16B_aligned():
         ek, ev = oracle.sort("u32", keys, vals)
         assert np.array_equal(to_host(dk, keys), ek) and np.array_equal(to_host(dv, vals), ev)
         assert int(big_k[:off].abs().sum()) == 0 and int(big_k[off + n:].abs().sum()) == 0
+
+
+# ---- the C++ drop-in header: the reference's own test program re-stated (harness/unittest.cpp) ----
+def test_cpp_harness_unittest_and_helloworld():
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([os.path.join(root, "harness", "helloworld")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "sorted" in r.stdout, r.stdout + r.stderr
+    r = subprocess.run([os.path.join(root, "harness", "unittest"), "32"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
+    assert "0 failed cases" in r.stdout
