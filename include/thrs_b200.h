@@ -104,6 +104,15 @@ THRS_API int thrs_sort_keys(thrs_sorter* s, void* keys, uint32_t n, void* temp,
 THRS_API int thrs_sort_pairs(thrs_sorter* s, void* keys, void* values, uint32_t n, void* temp,
                              int start_bits, int end_bits, void* stream);
 
+/* Digit histogram of one 8-bit window: counts[d] = #keys whose digit
+ * (getKeyBits(key) >> start_bit) & 0xFF is d, in sort order (descending sorters count
+ * the complemented digit).  The same single-read kernel the sort starts with
+ * (replaces blockCount, kernel.cu:73-103); used by the multi-GPU layer to pick
+ * MSD splitters.  `counts_out`: 256 uint32 in device memory; `temp`: at least
+ * thrs_temp_bytes(n).pSumBuffer bytes.  Asynchronous on `stream`. */
+THRS_API int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, int start_bit,
+                                  uint32_t* counts_out, void* temp, void* stream);
+
 /* Host-buffer convenience used for end-to-end timing: what unittest.cpp:399-414
  * does around a sort (thrs::Buffer alloc, H2D, sort, sync, D2H), in one call.
  * `values` may be NULL for a keys-only sort.  Blocking. */

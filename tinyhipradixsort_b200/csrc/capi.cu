@@ -139,6 +139,25 @@ int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out)
     return THRS_OK;
 }
 
+// first use on this process: device facts + opt-in to large dynamic shared memory
+static int prepare_device(thrs_sorter* s)
+{
+    std::call_once(s->prepared_once, [s]() {
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, dev);
+        for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[v]();
+        if (e == cudaSuccess) e = s->table->prepare_histogram();
+        s->prepared_err = e;
+    });
+    if (s->prepared_err != cudaSuccess) {
+        cudaGetLastError();
+        return fail(THRS_ERR_NO_DEVICE, "no usable CUDA device (%s); this library has no CPU fallback",
+                    cudaGetErrorString(s->prepared_err));
+    }
+    return THRS_OK;
+}
+
 static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint32_t n, void* temp, int start_bits,
                      int end_bits, cudaStream_t stream)
 {
@@ -161,19 +180,8 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     for (int b = start_bits; b < end_bits && b < key_bits; b += 8) ++passes;
     if (passes == 0) return THRS_OK;
 
-    std::call_once(s->prepared_once, [s]() {
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, dev);
-        for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[v]();
-        if (e == cudaSuccess) e = s->table->prepare_histogram();
-        s->prepared_err = e;
-    });
-    if (s->prepared_err != cudaSuccess) {
-        cudaGetLastError();
-        return fail(THRS_ERR_NO_DEVICE, "no usable CUDA device (%s); this library has no CPU fallback",
-                    cudaGetErrorString(s->prepared_err));
-    }
+    int prc = prepare_device(s);
+    if (prc) return prc;
 
     thrs_temp_def def;
     thrs_temp_bytes(s, n, &def);
@@ -271,6 +279,26 @@ int thrs_sort_pairs(thrs_sorter* s, void* keys, void* values, uint32_t n, void* 
                     void* stream)
 {
     return sort_impl(s, keys, values, true, n, temp, start_bits, end_bits, static_cast<cudaStream_t>(stream));
+}
+
+int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, int start_bit, uint32_t* counts_out, void* temp,
+                         void* stream_)
+{
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!s || !counts_out || !temp || (!keys && n)) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_digit_histogram: NULL argument");
+    if (start_bit < 0 || start_bit >= s->kbytes * 8) return fail(THRS_ERR_BIT_RANGE, "thrs_digit_histogram: start_bit outside the key");
+    int rc = prepare_device(s);
+    if (rc) return rc;
+    Scratch sc{static_cast<uint32_t*>(temp)};
+    CUDA_TRY(cudaMemsetAsync(temp, 0, 4ull * Scratch::CONTROL_WORDS, stream), "cudaMemsetAsync(scratch)");
+    if (n) {
+        const uint64_t nvec = (uint64_t)n * s->kbytes / 16;
+        uint64_t grid = div_up(nvec > 0 ? nvec : 1, (uint64_t)HIST_THREADS * 4);
+        if (grid > (uint64_t)s->sm_count) grid = s->sm_count;
+        CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bit, 1, sc, (int)grid, stream), "histogram_kernel launch");
+    }
+    CUDA_TRY(cudaMemcpyAsync(counts_out, sc.hist(), 4ull * RADIX, cudaMemcpyDeviceToDevice, stream), "copy histogram");
+    return THRS_OK;
 }
 
 static int grow(void** p, uint64_t* have, uint64_t need)

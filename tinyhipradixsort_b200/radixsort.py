@@ -209,6 +209,11 @@ class RadixSort:
                                          int(numberOfInputs), _ptr(temporaryBuffer), int(startBits),
                                          int(endBits), _stream(stream)))
 
+    def digitHistogram(self, keyBuffer, numberOfInputs, startBit, countsOut, temporaryBuffer, stream=None):
+        """256-bin histogram (uint32, device) of digit (getKeyBits(key) >> startBit) & 0xFF in sort order."""
+        _check(self._lib.thrs_digit_histogram(self._h, _ptr(keyBuffer), int(numberOfInputs), int(startBit),
+                                              _ptr(countsOut), _ptr(temporaryBuffer), _stream(stream)))
+
     # -- not in the reference: what unittest.cpp:399-414 does around a sort, in one C-ABI call
     def sortHost(self, host_keys, host_values, startBits, endBits):
         """Sort numpy arrays / CPU tensors in place (H2D, sort, D2H inside the call)."""
