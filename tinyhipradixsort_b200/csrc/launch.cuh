@@ -49,20 +49,57 @@ struct KernelTable {
     uint32_t tile_items[4];
 };
 
-template <class KeyT, int KIND, bool DESC>
-cudaError_t launch_histogram(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
-                             cudaStream_t stream)
+template <class KeyT, int KIND, bool DESC, int PASSES>
+cudaError_t launch_histogram_p(const void* keys, uint32_t n, uint32_t start_bit, Scratch sc, int grid, cudaStream_t stream)
 {
-    histogram_kernel<KeyT, KIND, DESC><<<grid, HIST_THREADS, HistShape<(int)sizeof(KeyT)>::BYTES, stream>>>(
-        static_cast<const KeyT*>(keys), n, start_bit, passes, sc);
+    histogram_kernel<KeyT, KIND, DESC, PASSES><<<grid, HIST_THREADS, HistShape<(int)sizeof(KeyT)>::BYTES, stream>>>(
+        static_cast<const KeyT*>(keys), n, start_bit, sc);
     return cudaGetLastError();
 }
 
 template <class KeyT, int KIND, bool DESC>
+cudaError_t launch_histogram(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
+                             cudaStream_t stream)
+{
+    switch (passes) {
+    case 1: return launch_histogram_p<KeyT, KIND, DESC, 1>(keys, n, start_bit, sc, grid, stream);
+    case 2: return launch_histogram_p<KeyT, KIND, DESC, 2>(keys, n, start_bit, sc, grid, stream);
+    case 3: return launch_histogram_p<KeyT, KIND, DESC, 3>(keys, n, start_bit, sc, grid, stream);
+    case 4: return launch_histogram_p<KeyT, KIND, DESC, 4>(keys, n, start_bit, sc, grid, stream);
+    default: break;
+    }
+    if (sizeof(KeyT) == 8) {
+        switch (passes) {
+        case 5: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 5 : 1>(keys, n, start_bit, sc, grid, stream);
+        case 6: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 6 : 1>(keys, n, start_bit, sc, grid, stream);
+        case 7: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 7 : 1>(keys, n, start_bit, sc, grid, stream);
+        case 8: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 8 : 1>(keys, n, start_bit, sc, grid, stream);
+        default: break;
+        }
+    }
+    return cudaErrorInvalidValue;
+}
+
+template <class KeyT, int KIND, bool DESC, int PASSES>
+cudaError_t prepare_histogram_p()
+{
+    return cudaFuncSetAttribute(histogram_kernel<KeyT, KIND, DESC, PASSES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)HistShape<(int)sizeof(KeyT)>::BYTES);
+}
+template <class KeyT, int KIND, bool DESC>
 cudaError_t prepare_histogram()
 {
-    return cudaFuncSetAttribute(histogram_kernel<KeyT, KIND, DESC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)HistShape<(int)sizeof(KeyT)>::BYTES);
+    cudaError_t e = prepare_histogram_p<KeyT, KIND, DESC, 1>();
+    if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, 2>();
+    if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, 3>();
+    if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, 4>();
+    if (sizeof(KeyT) == 8) {
+        if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 5 : 1>();
+        if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 6 : 1>();
+        if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 7 : 1>();
+        if (e == cudaSuccess) e = prepare_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 8 : 1>();
+    }
+    return e;
 }
 
 template <class KeyT, int KIND, bool DESC, int VBYTES>
