@@ -20,7 +20,7 @@ and step 5 keeps source order.  Counts are 64-bit at this layer (2^32 pairs do n
 uint32 n of the single-GPU API); a rank's share must stay below 2^32 items.
 
 The local device work is injected (`LocalOps`) so that the host logic — splitters, count
-matrices, the exchange — can be exercised on CPU with gloo in tests/ (where the oracle stands in
+matrices, the exchange — can be exercised on CPU with gloo in tests/ (where a CPU checker stands in
 for the kernels).  The product default is `CudaLocalOps`; nothing falls back automatically.
 """
 import numpy as np
