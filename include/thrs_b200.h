@@ -145,6 +145,20 @@ typedef struct thrs_profile {
 THRS_API int thrs_profile_enable(thrs_sorter* s, int on);
 THRS_API int thrs_profile_read(thrs_sorter* s, thrs_profile* out);
 
+/* Ranking used by the onesweep kernels (no counterpart in the reference, which has one scheme,
+ * kernel.cu:293-345).  COUNTER_RETURN takes the old value of a returning shared-memory atomicAdd
+ * as the stable rank; it is exact only where lanes that hit one counter in one warp instruction
+ * are served in ascending lane order, which a device probe checks on first use.  AUTO (default)
+ * = COUNTER_RETURN if the probe found no group out of order, else MATCH_MASK (order-free).
+ * Both run on the GPU; neither is a fallback to the host. */
+#define THRS_RANKING_AUTO 0
+#define THRS_RANKING_MATCH_MASK 1
+#define THRS_RANKING_COUNTER_RETURN 2
+THRS_API int thrs_set_ranking(thrs_sorter* s, int ranking);
+/* ranking_in_use: THRS_RANKING_MATCH_MASK or _COUNTER_RETURN; probe_in_order: 1 if the device
+ * probe passed; probe_groups: multi-lane groups the probe checked.  Needs a device. */
+THRS_API int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in_order, uint64_t* probe_groups);
+
 /* Diagnostics. */
 THRS_API const char* thrs_last_error(void);        /* thread-local text of the last failure */
 THRS_API const char* thrs_version(void);

@@ -79,12 +79,79 @@ __global__ void __launch_bounds__(512) k(uint32_t* out, int distinct_mask)
             uint32_t h = hash(x); s[h & 8191] = x; s[(h >> 8) & 8191] = x; s[(h >> 16) & 8191] = x; s[(h >> 19) & 8191] = x;
         } else if (MODE == 21) { // 4 random LDS over 8192 words
             uint32_t h = hash(x); acc += s[h & 8191] + s[(h >> 8) & 8191] + s[(h >> 16) & 8191] + s[(h >> 19) & 8191];
+        } else if (MODE == 30) { // 8 independent ballots, no match logic (VOTE throughput)
+            uint32_t v = 0;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) v ^= __ballot_sync(0xffffffffu, (d >> b) & 1);
+            acc += v;
+        } else if (MODE == 31) { // counter-return ranking: ATOMS ret + LDS, groups fixed by a ballot loop
+            uint32_t old = atomicAdd(&my[d], 1u);
+            __syncwarp();
+            uint32_t cur = my[d];
+            uint32_t rank = old;
+            uint32_t multi = __ballot_sync(0xffffffffu, cur != old + 1u);
+            while (multi) {
+                int L = __ffs(multi) - 1;
+                uint32_t dL = __shfl_sync(0xffffffffu, d, L);
+                uint32_t grp = __ballot_sync(0xffffffffu, d == dL);
+                if (d == dL) rank = cur - __popc(grp) + __popc(grp & lt);
+                multi &= ~grp;
+            }
+            acc += rank;
+            __syncwarp();
+        } else if (MODE == 32) { // MODE 31 + base lookup + 64-bit staging store
+            uint32_t old = atomicAdd(&my[d], 1u);
+            __syncwarp();
+            uint32_t cur = my[d];
+            uint32_t rank = old;
+            uint32_t multi = __ballot_sync(0xffffffffu, cur != old + 1u);
+            while (multi) {
+                int L = __ffs(multi) - 1;
+                uint32_t dL = __shfl_sync(0xffffffffu, d, L);
+                uint32_t grp = __ballot_sync(0xffffffffu, d == dL);
+                if (d == dL) rank = cur - __popc(grp) + __popc(grp & lt);
+                multi &= ~grp;
+            }
+            __syncwarp();
+            uint32_t base = s[16 * 256 + warp * 256 + ((d * 5 + 1) & 255)];
+            uint2* st = (uint2*)(s + 16 * 256);
+            st[(hash(x) + base + rank) & 4095] = make_uint2(x, rank);
+        } else if (MODE == 33) { // present kernel's step: ATOMS count + atomicOr mask + LDS.64 + leader STS.64 + 64-bit staging store
+            uint2* m2 = (uint2*)s + warp * 256;
+            atomicAdd(&m2[(d * 7 + 3) & 255].y, 1u);
+            atomicOr(&m2[d].x, 1u << lane);
+            __syncwarp();
+            uint2 e = m2[d];
+            uint32_t lower = __popc(e.x & lt);
+            __syncwarp();
+            if (lower == 0) m2[d] = make_uint2(0u, e.y + __popc(e.x));
+            __syncwarp();
+            uint2* st = (uint2*)(s + 16 * 256);
+            st[(hash(x) + e.y + lower) & 4095] = make_uint2(x, lower);
+        } else if (MODE == 34) { // 8-ballot match + leader ATOMS ret + shfl broadcast (CUB-like) + staging store
+            uint32_t peers = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) { bool p = (d >> b) & 1; uint32_t m = __ballot_sync(0xffffffffu, p); peers &= p ? m : ~m; }
+            uint32_t lower = __popc(peers & lt);
+            uint32_t base = 0;
+            if (lower == 0) base = atomicAdd(&my[d], __popc(peers));
+            base = __shfl_sync(0xffffffffu, base, __ffs(peers) - 1);
+            uint2* st = (uint2*)(s + 16 * 256);
+            st[(hash(x) + base + lower) & 4095] = make_uint2(x, lower);
+        } else if (MODE == 35) { // staging store only (64-bit random into 4096 slots)
+            uint2* st = (uint2*)(s + 16 * 256);
+            st[hash(x) & 4095] = make_uint2(x, d);
+        } else if (MODE == 36) { // counter-return step: ATOMS count + ATOMS.ADD ret position + 64-bit staging store
+            atomicAdd(&my[(d * 7 + 3) & 255], 1u);
+            uint32_t pos = atomicAdd(&my[d], 1u);
+            uint2* st = (uint2*)(s + 16 * 256);
+            st[(hash(x) + pos) & 4095] = make_uint2(x, pos);
         } else if (MODE == 8) { // atomicOr match-mask (reference's scheme)
             atomicOr(&my[d], 1u << lane); __syncwarp(); uint32_t m = my[d]; acc += __popc(m & lt); __syncwarp(); if ((m & lt) == 0) my[d] = 0; __syncwarp();
         }
     }
     if (acc == 0x12345678u) out[0] = acc + s[threadIdx.x];
-    __syncthreads(); if ((MODE >= 2 && MODE <= 4) || MODE >= 15) { if (blockIdx.x == 0) out[2 + (threadIdx.x & 7)] = s[threadIdx.x * 7] + s[threadIdx.x + 4096]; }
+    __syncthreads(); if ((MODE >= 2 && MODE <= 4) || MODE >= 15 || MODE == 8) { if (blockIdx.x == 0) out[2 + (threadIdx.x & 7)] = s[threadIdx.x * 7] + s[threadIdx.x + 4096]; }
 }
 
 template <int MODE>
@@ -129,6 +196,13 @@ int main()
         run<12>("4 LDS random", mask, out);
         run<13>("4 ATOMS random", mask, out);
         run<14>("ballot match + 4 LDS random", mask, out);
+        run<30>("8 ballots only", mask, out);
+        run<31>("counter-return rank + group ballots", mask, out);
+        run<32>("counter-return rank + base + stage", mask, out);
+        run<33>("present step (2 ATOMS+LDS64+STS64+stage)", mask, out);
+        run<34>("8-ballot + leader ATOMS + shfl + stage", mask, out);
+        run<35>("stage only (STS.64 random)", mask, out);
+        run<36>("counter-return step (2 ATOMS + stage)", mask, out);
     }
     cudaError_t e = cudaDeviceSynchronize();
     printf("%s\n", cudaGetErrorString(e));

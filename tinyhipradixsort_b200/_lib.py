@@ -67,6 +67,9 @@ SIGNATURES = {
     "thrs_version": (ctypes.c_char_p, []),
     "thrs_last_launch_count": (ctypes.c_int, []),
     "thrs_tile_items": (ctypes.c_uint32, [ctypes.c_void_p]),
+    "thrs_set_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "thrs_get_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),
+                                        ctypes.POINTER(ctypes.c_uint64)]),
 }
 
 _lib = None

@@ -14,6 +14,7 @@
 
 #include "../../include/thrs_b200.h"
 #include "launch.cuh"
+#include "probe.cuh"
 
 using namespace thrs_b200;
 
@@ -57,6 +58,11 @@ struct thrs_sorter {
     std::once_flag prepared_once;
     cudaError_t prepared_err = cudaSuccess;
     int sm_count = 148;
+    // ranking of the onesweep kernels: requested (THRS_RANKING_*) and resolved (0 match-mask, 1 counter-return)
+    int ranking_request = THRS_RANKING_AUTO;
+    int fast = 0;
+    int probe_in_order = 0;
+    unsigned long long probe_groups = 0;
     // workspace of thrs_sort_host (grown on demand, guarded)
     std::mutex host_mu;
     void* ws_keys = nullptr;
@@ -122,16 +128,22 @@ void thrs_destroy(thrs_sorter* s)
     delete s;
 }
 
-uint32_t thrs_tile_items(const thrs_sorter* s) { return s ? s->table->tile_items[s->vslot] : 0; }
+uint32_t thrs_tile_items(const thrs_sorter* s) { return s ? s->table->tile_items[s->fast][s->vslot] : 0; }
 
 int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out)
 {
     if (!s || !out) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_temp_bytes: NULL argument");
     // One layout serves sortKeys and sortPairs of this sorter: size the status rows for
     // the smaller of the two tile shapes.  Pure, monotone function of n (hpp:859).
-    const uint32_t t_keys = s->table->tile_items[0];
-    const uint32_t t_pairs = s->table->tile_items[s->vslot];
-    const uint64_t tiles = div_up(n, t_keys < t_pairs ? t_keys : t_pairs);
+    // ... and of both rankings, so the size does not depend on what the device probe decides.
+    uint32_t t_min = 0xffffffffu;
+    for (int f = 0; f < 2; ++f) {
+        const uint32_t t_keys = s->table->tile_items[f][0];
+        const uint32_t t_pairs = s->table->tile_items[f][s->vslot];
+        if (t_keys < t_min) t_min = t_keys;
+        if (t_pairs < t_min) t_min = t_pairs;
+    }
+    const uint64_t tiles = div_up(n, t_min);
     const uint64_t passes = (uint64_t)s->kbytes; // key bits / 8
     out->pSumBuffer = align16(4ull * (Scratch::CONTROL_WORDS + passes * Scratch::pass_words(tiles)));
     out->keyOutBuffer = align16((uint64_t)s->kbytes * n);
@@ -146,8 +158,25 @@ static int prepare_device(thrs_sorter* s)
         int dev = 0;
         cudaError_t e = cudaGetDevice(&dev);
         if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, dev);
-        for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[v]();
+        for (int f = 0; f < 2; ++f)
+            for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[f][v]();
         if (e == cudaSuccess) e = s->table->prepare_histogram();
+        // which ranking this device can run exactly (probe.cuh); once per process and device
+        if (e == cudaSuccess) {
+            static std::mutex mu;
+            static int cached[64];          // 0 unknown, 1 out of order, 2 in order
+            static unsigned long long cached_groups[64];
+            std::lock_guard<std::mutex> lock(mu);
+            const int slot = dev & 63;
+            if (cached[slot] == 0) {
+                int ok = 0;
+                unsigned long long groups = 0;
+                e = run_rank_order_probe(s->sm_count, &ok, &groups);
+                if (e == cudaSuccess) { cached[slot] = ok ? 2 : 1; cached_groups[slot] = groups; }
+            }
+            s->probe_in_order = cached[slot] == 2;
+            s->probe_groups = cached_groups[slot];
+        }
         s->prepared_err = e;
     });
     if (s->prepared_err != cudaSuccess) {
@@ -182,6 +211,9 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
 
     int prc = prepare_device(s);
     if (prc) return prc;
+    // counter-return ranking only where the probe found the hardware order it needs
+    s->fast = (s->ranking_request == THRS_RANKING_MATCH_MASK) ? 0
+              : (s->ranking_request == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
 
     thrs_temp_def def;
     thrs_temp_bytes(s, n, &def);
@@ -190,7 +222,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     char* val_out = key_out + def.keyOutBuffer;
 
     const int vslot = pairs ? s->vslot : 0;
-    const uint32_t tile = s->table->tile_items[vslot];
+    const uint32_t tile = s->table->tile_items[s->fast][vslot];
     const uint64_t tiles_total = div_up(n, tile);
     const uint64_t part_items = (uint64_t)(VALUE_MASK / tile) * tile; // < 2^30, whole tiles
     const int parts = (int)div_up(n, part_items);
@@ -245,9 +277,10 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
             a.gsum = sc.gsum(p, tiles_total) + group0 * RADIX;
             a.gprefix = sc.gprefix(p, tiles_total) + group0 * RADIX;
             a.ticket = sc.ticket(p, q);
+            a.sm_count = s->sm_count;
             a.base_in = sc.base(p, q);
             a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;
-            CUDA_TRY(s->table->onesweep[vslot](a, stream), "onesweep_kernel launch");
+            CUDA_TRY(s->table->onesweep[s->fast][vslot](a, stream), "onesweep_kernel launch");
             ++g_launches;
         }
         CUDA_TRY(mark(), "profile event");
@@ -385,6 +418,28 @@ int thrs_profile_read(thrs_sorter* s, thrs_profile* out)
 }
 
 const char* thrs_last_error(void) { return g_err; }
+int thrs_set_ranking(thrs_sorter* s, int ranking)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_ranking: NULL sorter");
+    if (ranking < THRS_RANKING_AUTO || ranking > THRS_RANKING_COUNTER_RETURN)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_ranking: bad ranking");
+    s->ranking_request = ranking;
+    return THRS_OK;
+}
+
+int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in_order, uint64_t* probe_groups)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_get_ranking: NULL sorter");
+    int rc = prepare_device(s);
+    if (rc) return rc;
+    const int fast = (s->ranking_request == THRS_RANKING_MATCH_MASK) ? 0
+                     : (s->ranking_request == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
+    if (ranking_in_use) *ranking_in_use = fast ? THRS_RANKING_COUNTER_RETURN : THRS_RANKING_MATCH_MASK;
+    if (probe_in_order) *probe_in_order = s->probe_in_order;
+    if (probe_groups) *probe_groups = s->probe_groups;
+    return THRS_OK;
+}
+
 const char* thrs_version(void) { return "thrs_b200 0.1 (sm_100a onesweep)"; }
 int thrs_last_launch_count(void) { return g_launches; }
 

@@ -287,11 +287,13 @@ template <int VBYTES> struct ValueOf { using type = uint32_t; };
 template <> struct ValueOf<8> { using type = uint2; };
 template <> struct ValueOf<16> { using type = uint4; };
 
-template <class KeyT, int VBYTES, int THREADS, int ITEMS>
+// FAST selects the counter-return ranking (one 32-bit counter per warp and digit) instead of the
+// match-mask ranking ({mask, base} pairs); see onesweep_tile.
+template <class KeyT, int VBYTES, int THREADS, int ITEMS, bool FAST>
 struct OnesweepSmem {
     static constexpr int WARPS = THREADS / 32;
     static constexpr int TILE = THREADS * ITEMS;
-    static constexpr size_t TBL_BYTES = (size_t)WARPS * RADIX * 8;
+    static constexpr size_t TBL_BYTES = (size_t)WARPS * RADIX * (FAST ? 4 : 8);
     static constexpr size_t KEY_BYTES = (size_t)TILE * sizeof(KeyT);
     static constexpr size_t VAL_BYTES = (size_t)TILE * VBYTES;
     static constexpr size_t OFF_TBL = 0;
@@ -301,17 +303,38 @@ struct OnesweepSmem {
     static constexpr size_t BYTES = OFF_BIN + RADIX * 4 + 64;
 };
 
-template <bool FULL, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
-__device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+// Keys of one tile into registers, warp-striped.  `valid` == TILE takes the unguarded path.
+template <class KeyT, int THREADS, int ITEMS>
+__device__ __forceinline__ void load_tile_keys(KeyT (&key)[ITEMS], const KeyT* __restrict__ keys_in, size_t tile_base,
+                                               uint32_t valid)
+{
+    const uint32_t my0 = (threadIdx.x >> 5) * (32 * ITEMS) + (threadIdx.x & 31);
+    const KeyT* kin = keys_in + tile_base + my0;
+    if (valid == (uint32_t)(THREADS * ITEMS)) {
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) key[j] = kin[j * 32];
+    } else {
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) key[j] = (my0 + j * 32 < valid) ? kin[j * 32] : KeyT(0);
+    }
+}
+
+// One tile.  `key` holds the tile's keys on entry and the NEXT tile's keys on return (they are
+// requested as soon as this tile's keys are staged, so their latency and the ticket's hide behind
+// the look-back and the read-out).  Returns the next tile's ticket.
+template <bool FULL, bool FAST, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
+__device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT* __restrict__ keys_in, uint32_t n,
+                                              uint32_t num_tiles, uint32_t* __restrict__ ticket,
+                                              KeyT* __restrict__ keys_out,
                                               const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
                                               typename ValueOf<VBYTES>::type* __restrict__ vals_out, uint32_t bit,
-                                              uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
+                                              uint32_t bit_c, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
                                               uint32_t* __restrict__ gprefix, const uint32_t* __restrict__ base_in,
                                               uint32_t* __restrict__ base_out, uint32_t tile, bool last_tile,
                                               size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw)
 {
     using ValT = typename ValueOf<VBYTES>::type;
-    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS>;
+    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST>;
     constexpr int WARPS = SM::WARPS;
     constexpr bool PAIRS = VBYTES > 0;
     // 4-byte key + 4-byte value travel through shared memory as one 8-byte element: a random
@@ -329,17 +352,19 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
     const int lane = tid & 31;
     const int warp = tid >> 5;
     uint2* tw = tbl + warp * RADIX;
+    // The two words of a cell swap places every 16 digits, so the 32-bit accesses to "mask" (or to
+    // "base") of 32 consecutive digits fall in 32 different banks instead of the 16 even (odd) ones.
+    uint32_t* tbl32 = reinterpret_cast<uint32_t*>(tbl);
+    uint32_t* tw32 = reinterpret_cast<uint32_t*>(tw);
+    auto mask_word = [](uint32_t d) { return 2u * d + ((d >> 4) & 1u); };
+    auto base_word = [](uint32_t d) { return FAST ? d : 2u * d + (((d >> 4) & 1u) ^ 1u); };
+    constexpr int ROW = FAST ? RADIX : 2 * RADIX; // 32-bit words per warp row
+    if (FAST) tw32 = tbl32 + warp * RADIX;
 
     PHASE_BEGIN();
-    // ---- load keys (warp-striped, coalesced)
-    KeyT key[ITEMS];
     const uint32_t my0 = warp * (32 * ITEMS) + lane;
-    const KeyT* kin = keys_in + tile_base + my0;
-#pragma unroll
-    for (int j = 0; j < ITEMS; ++j) {
-        if (FULL || my0 + j * 32 < tile_valid) key[j] = kin[j * 32];
-        else key[j] = KeyT(0);
-    }
+    // ticket of the tile after this one: requested now, read after the scan's barriers
+    if (tid == 0) s_misc[14] = atomicAdd(ticket, 1u);
 
     // ---- phase A: per-warp digit counts
 #ifdef THRS_PHASE_TIMING
@@ -348,7 +373,10 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
 #endif
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
-        if (FULL || my0 + j * 32 < tile_valid) atomicAdd(&tw[digit_of<KIND, DESC>(key[j], bit)].y, 1u);
+        if (FULL || my0 + j * 32 < tile_valid) {
+            const uint32_t d = digit_of<KIND, DESC>(key[j], bit);
+            atomicAdd(tw32 + base_word(d), 1u);
+        }
     }
 
     // values are requested now; their latency hides behind the scan
@@ -369,24 +397,23 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
     uint32_t count = 0, bin_start;
     uint32_t* my_status = status + (size_t)tile * RADIX + tid;
     {
-        uint32_t c[WARPS];
         if (tid < RADIX) {
 #pragma unroll
-            for (int w = 0; w < WARPS; ++w) {
-                c[w] = tbl[w * RADIX + tid].y;
-                count += c[w];
-            }
+            for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
             // early publication: successors can start summing while this tile still ranks
             st_relaxed(my_status, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
             atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
         }
         bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
         if (tid < RADIX) {
+            // the counts are read a second time (conflict-free) rather than held in 16 registers
             uint32_t run = bin_start;
 #pragma unroll
             for (int w = 0; w < WARPS; ++w) {
-                tbl[w * RADIX + tid].y = run;
-                run += c[w];
+                uint32_t* cell = tbl32 + w * ROW + base_word(tid);
+                const uint32_t c = *cell;
+                *cell = run;
+                run += c;
             }
         }
     }
@@ -399,22 +426,50 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         const bool ok = FULL || my0 + j * 32 < tile_valid;
-        const uint32_t d = digit_of<KIND, DESC>(key[j], bit);
-        if (ok) atomicOr(&tw[d].x, lane_bit);
-        __syncwarp();
-        uint2 e = make_uint2(0u, 0u);
-        if (ok) e = tw[d];
-        const uint32_t lower = __popc(e.x & lane_lt);
-        __syncwarp();
-        if (ok && lower == 0) tw[d] = make_uint2(0u, e.y + __popc(e.x));
-        __syncwarp();
+        // bit_c == bit, passed as a second kernel parameter: ptxas cannot prove it and so does not
+        // keep phase A's 16 digit/address temporaries alive (and spill around them) until here
+        const uint32_t d = digit_of<KIND, DESC>(key[j], bit_c);
+        uint32_t pos;
+        if (FAST) {
+            // counter-return ranking: the returning atomic hands the lanes that share a counter
+            // consecutive old values in ascending lane order (probed at thrs_create, probe.cuh),
+            // so the old value IS the stable tile-sorted position.
+            pos = 0;
+            if (ok) pos = atomicAdd(tw32 + d, 1u);
+            __syncwarp();
+        } else {
+            const bool swapped = (d >> 4) & 1u;
+            if (ok) atomicOr(tw32 + mask_word(d), lane_bit);
+            __syncwarp();
+            uint2 e = make_uint2(0u, 0u);
+            if (ok) {
+                const uint2 raw = tw[d];
+                e = swapped ? make_uint2(raw.y, raw.x) : raw;
+            }
+            const uint32_t lower = __popc(e.x & lane_lt);
+            __syncwarp();
+            if (ok && lower == 0) {
+                const uint32_t nb = e.y + __popc(e.x);
+                tw[d] = swapped ? make_uint2(nb, 0u) : make_uint2(0u, nb);
+            }
+            __syncwarp();
+            pos = e.y + lower;
+        }
         if (ok) {
-            if (PACKED) s_kv[e.y + lower] = make_uint2((uint32_t)key[j], val32(val[j]));
+            if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
             else {
-                s_keys[e.y + lower] = key[j];
-                if (PAIRS) s_vals[e.y + lower] = val[j];
+                s_keys[pos] = key[j];
+                if (PAIRS) s_vals[pos] = val[j];
             }
         }
+    }
+
+    // ---- this tile's keys are staged: request the next tile's into the same registers
+    const uint32_t next_tile = s_misc[14];
+    if (next_tile < num_tiles) {
+        const size_t nb = (size_t)next_tile * (size_t)(THREADS * ITEMS);
+        const uint32_t nv = (n - nb) < (size_t)(THREADS * ITEMS) ? (uint32_t)(n - nb) : (uint32_t)(THREADS * ITEMS);
+        load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, nb, nv);
     }
 
     PHASE_MARK(4);
@@ -499,44 +554,59 @@ __device__ __forceinline__ void onesweep_tile(const KeyT* __restrict__ keys_in, 
             }
         }
     }
+    // the per-warp tables must be zero again for the next tile's phase A
+    {
+        uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
+#pragma unroll
+        for (int i = tid; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
     PHASE_MARK(7);
+    return next_tile;
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB>
+template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
                 typename ValueOf<VBYTES>::type* __restrict__ vals_out,
-                uint32_t n, uint32_t bit, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
+                uint32_t n, uint32_t bit, uint32_t bit_c, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
                 uint32_t* __restrict__ gprefix, uint32_t* __restrict__ ticket,
                 const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out)
 {
-    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS>;
+    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST>;
     static_assert((uint64_t)GROUP_TILES * SM::TILE < (1ull << GROUP_SUM_BITS), "group accumulator overflow");
     constexpr int TILE = SM::TILE;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* s_misc = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN) + RADIX;
 
-    // ---- tile ticket: tiles are processed in ticket order, so a tile only ever waits on
-    // tiles that already started (no deadlock whatever the block scheduler does)
+    // ---- persistent blocks: tiles are handed out by an atomic ticket, so a tile only ever waits
+    // on tiles that already started (no deadlock whatever the block scheduler does)
     if (threadIdx.x == 0) s_misc[15] = atomicAdd(ticket, 1u);
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
         for (int i = threadIdx.x; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
     __syncthreads();
-    const uint32_t tile = s_misc[15];
+    uint32_t tile = s_misc[15];
     const uint32_t num_tiles = (n + TILE - 1) / TILE;
-    const size_t tile_base = (size_t)tile * TILE;
-    const uint32_t tile_valid = (n - tile_base) < (size_t)TILE ? (uint32_t)(n - tile_base) : (uint32_t)TILE;
-    if (tile_valid == (uint32_t)TILE)
-        onesweep_tile<true, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(keys_in, keys_out, vals_in, vals_out, bit, status,
-                                                                      gsum, gprefix, base_in, base_out, tile, tile == num_tiles - 1,
-                                                                      tile_base, tile_valid, smem_raw);
-    else
-        onesweep_tile<false, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(keys_in, keys_out, vals_in, vals_out, bit, status,
-                                                                       gsum, gprefix, base_in, base_out, tile, tile == num_tiles - 1,
-                                                                       tile_base, tile_valid, smem_raw);
+    KeyT key[ITEMS];
+    if (tile < num_tiles) {
+        const size_t tb = (size_t)tile * TILE;
+        load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, tb, (n - tb) < (size_t)TILE ? (uint32_t)(n - tb) : (uint32_t)TILE);
+    }
+    while (tile < num_tiles) {
+        const size_t tile_base = (size_t)tile * TILE;
+        const uint32_t tile_valid = (n - tile_base) < (size_t)TILE ? (uint32_t)(n - tile_base) : (uint32_t)TILE;
+        if (tile_valid == (uint32_t)TILE)
+            tile = onesweep_tile<true, FAST, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
+                key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
+                base_out, tile, tile == num_tiles - 1, tile_base, tile_valid, smem_raw);
+        else
+            tile = onesweep_tile<false, FAST, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
+                key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
+                base_out, tile, tile == num_tiles - 1, tile_base, tile_valid, smem_raw);
+    }
 }
 
 } // namespace thrs_b200

@@ -7,22 +7,23 @@
 
 namespace thrs_b200 {
 
-// Tile shape per (key bytes, value bytes).  THREADS x ITEMS items per tile; MINB = resident
-// blocks per SM the register allocation is bounded for.
+// Tile shape per (key bytes, value bytes, ranking).  THREADS x ITEMS items per tile; MINB = resident
+// blocks per SM the register allocation is bounded for.  FAST = counter-return ranking (4-byte
+// table cells), otherwise match-mask ranking (8-byte cells).
 #ifndef THRS_TUNE_THREADS
-#define THRS_TUNE_THREADS 512
-#define THRS_TUNE_ITEMS 16
-#define THRS_TUNE_MINB 2
+#define THRS_TUNE_THREADS 256
+#define THRS_TUNE_ITEMS 28
+#define THRS_TUNE_MINB 3
 #endif
-template <int KBYTES, int VBYTES> struct Tuning {
+template <int KBYTES, int VBYTES, bool FAST> struct Tuning {
     static constexpr int THREADS = THRS_TUNE_THREADS, ITEMS = THRS_TUNE_ITEMS, MINB = THRS_TUNE_MINB;
 };
-template <> struct Tuning<4, 8> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
-template <> struct Tuning<4, 16> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
-template <> struct Tuning<8, 0> { static constexpr int THREADS = 512, ITEMS = 12, MINB = 2; };
-template <> struct Tuning<8, 4> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
-template <> struct Tuning<8, 8> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
-template <> struct Tuning<8, 16> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
+template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
+template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
+template <bool FAST> struct Tuning<8, 0, FAST> { static constexpr int THREADS = 512, ITEMS = 12, MINB = 2; };
+template <bool FAST> struct Tuning<8, 4, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
+template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
+template <bool FAST> struct Tuning<8, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
 
 struct OnesweepArgs {
     const void* keys_in;
@@ -35,6 +36,7 @@ struct OnesweepArgs {
     uint32_t* gsum;    // [groups][256] group accumulators of this part
     uint32_t* gprefix; // [groups][256] prefix through the previous group
     uint32_t* ticket;
+    int sm_count;
     const uint32_t* base_in;
     uint32_t* base_out;
 };
@@ -43,10 +45,11 @@ struct KernelTable {
     // value slot: 0 = keys only, 1 = 4-byte, 2 = 8-byte, 3 = 16-byte values
     cudaError_t (*histogram)(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
                              cudaStream_t stream);
-    cudaError_t (*onesweep[4])(const OnesweepArgs& a, cudaStream_t stream);
-    cudaError_t (*prepare[4])(); // opt in to > 48 KiB dynamic shared memory
+    // first index: 0 = match-mask ranking, 1 = counter-return ranking
+    cudaError_t (*onesweep[2][4])(const OnesweepArgs& a, cudaStream_t stream);
+    cudaError_t (*prepare[2][4])(); // opt in to > 48 KiB dynamic shared memory
     cudaError_t (*prepare_histogram)();
-    uint32_t tile_items[4];
+    uint32_t tile_items[2][4];
 };
 
 template <class KeyT, int KIND, bool DESC, int PASSES>
@@ -102,42 +105,50 @@ cudaError_t prepare_histogram()
     return e;
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST>
 cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
 {
-    using T = Tuning<(int)sizeof(KeyT), VBYTES>;
-    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS>;
+    using T = Tuning<(int)sizeof(KeyT), VBYTES, FAST>;
+    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST>;
     using ValT = typename ValueOf<VBYTES>::type;
     const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
-    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB><<<tiles, T::THREADS, SM::BYTES, stream>>>(
+    // persistent blocks, T::MINB per SM; correctness does not depend on all of them being resident
+    const uint32_t cap = (uint32_t)a.sm_count * T::MINB;
+    const uint32_t grid = tiles < cap ? tiles : cap;
+    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST><<<grid, T::THREADS, SM::BYTES, stream>>>(
         static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
-        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out);
+        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out);
     return cudaGetLastError();
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST>
 cudaError_t prepare_onesweep()
 {
-    using T = Tuning<(int)sizeof(KeyT), VBYTES>;
-    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS>;
-    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB>,
+    using T = Tuning<(int)sizeof(KeyT), VBYTES, FAST>;
+    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST>;
+    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES);
 }
+
+template <int KB, int VB, bool FAST> constexpr uint32_t tile_of() { return (uint32_t)(Tuning<KB, VB, FAST>::THREADS * Tuning<KB, VB, FAST>::ITEMS); }
 
 template <class KeyT, int KIND, bool DESC>
 const KernelTable* make_table()
 {
+    constexpr int KB = (int)sizeof(KeyT);
     static const KernelTable t = {
         &launch_histogram<KeyT, KIND, DESC>,
-        {&launch_onesweep<KeyT, KIND, DESC, 0>, &launch_onesweep<KeyT, KIND, DESC, 4>,
-         &launch_onesweep<KeyT, KIND, DESC, 8>, &launch_onesweep<KeyT, KIND, DESC, 16>},
-        {&prepare_onesweep<KeyT, KIND, DESC, 0>, &prepare_onesweep<KeyT, KIND, DESC, 4>,
-         &prepare_onesweep<KeyT, KIND, DESC, 8>, &prepare_onesweep<KeyT, KIND, DESC, 16>},
+        {{&launch_onesweep<KeyT, KIND, DESC, 0, false>, &launch_onesweep<KeyT, KIND, DESC, 4, false>,
+          &launch_onesweep<KeyT, KIND, DESC, 8, false>, &launch_onesweep<KeyT, KIND, DESC, 16, false>},
+         {&launch_onesweep<KeyT, KIND, DESC, 0, true>, &launch_onesweep<KeyT, KIND, DESC, 4, true>,
+          &launch_onesweep<KeyT, KIND, DESC, 8, true>, &launch_onesweep<KeyT, KIND, DESC, 16, true>}},
+        {{&prepare_onesweep<KeyT, KIND, DESC, 0, false>, &prepare_onesweep<KeyT, KIND, DESC, 4, false>,
+          &prepare_onesweep<KeyT, KIND, DESC, 8, false>, &prepare_onesweep<KeyT, KIND, DESC, 16, false>},
+         {&prepare_onesweep<KeyT, KIND, DESC, 0, true>, &prepare_onesweep<KeyT, KIND, DESC, 4, true>,
+          &prepare_onesweep<KeyT, KIND, DESC, 8, true>, &prepare_onesweep<KeyT, KIND, DESC, 16, true>}},
         &prepare_histogram<KeyT, KIND, DESC>,
-        {(uint32_t)(Tuning<(int)sizeof(KeyT), 0>::THREADS * Tuning<(int)sizeof(KeyT), 0>::ITEMS),
-         (uint32_t)(Tuning<(int)sizeof(KeyT), 4>::THREADS * Tuning<(int)sizeof(KeyT), 4>::ITEMS),
-         (uint32_t)(Tuning<(int)sizeof(KeyT), 8>::THREADS * Tuning<(int)sizeof(KeyT), 8>::ITEMS),
-         (uint32_t)(Tuning<(int)sizeof(KeyT), 16>::THREADS * Tuning<(int)sizeof(KeyT), 16>::ITEMS)}};
+        {{tile_of<KB, 0, false>(), tile_of<KB, 4, false>(), tile_of<KB, 8, false>(), tile_of<KB, 16, false>()},
+         {tile_of<KB, 0, true>(), tile_of<KB, 4, true>(), tile_of<KB, 8, true>(), tile_of<KB, 16, true>()}}};
     return &t;
 }
 

@@ -236,6 +236,18 @@ class RadixSort:
                 "pass_ms": [p.pass_ms[i] for i in range(p.passes)], "copyback_ms": p.copyback_ms,
                 "total_ms": p.total_ms, "passes": p.passes, "parts": p.parts}
 
+    RANKING_AUTO, RANKING_MATCH_MASK, RANKING_COUNTER_RETURN = 0, 1, 2
+
+    def setRanking(self, ranking):
+        """Choose the onesweep ranking (thrs_set_ranking); AUTO lets the device probe decide."""
+        _check(self._lib.thrs_set_ranking(self._h, int(ranking)))
+
+    def getRanking(self):
+        """(ranking in use, probe passed, groups the probe checked) — needs a device."""
+        r, ok, g = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_uint64(0)
+        _check(self._lib.thrs_get_ranking(self._h, ctypes.byref(r), ctypes.byref(ok), ctypes.byref(g)))
+        return r.value, bool(ok.value), int(g.value)
+
     def tileItems(self):
         return int(self._lib.thrs_tile_items(self._h))
 
