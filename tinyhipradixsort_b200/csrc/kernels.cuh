@@ -565,6 +565,23 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
     return next_tile;
 }
 
+// ---------------------------------------------------------------------------------------
+// onesweep_kernel — persistent blocks, software-pipelined over tiles.
+//
+// Per iteration a block works on two tiles at once, `tile` (current) and `prev`:
+//     phase A(tile)                      per-warp digit counts (keys were prefetched)
+//     scan(tile)                         publish the aggregate, per-warp bases
+//     resolve(prev)                      consume prev's look-back loads (issued one iteration ago)
+//     read-out(prev)                     coalesced stores from the staging buffer
+//     phase C(tile)                      rank + stage
+//     issue look-back loads(tile), prefetch keys(next tile)
+// so the ~2 us a status read takes under load, the key loads and the ticket round trip all
+// overlap phase A and the scan of the following tile instead of stalling the block.  A tile's
+// inclusive prefix is published one half-iteration later than in a straight-line kernel; its
+// aggregate (what successors mostly consume) is published as early as before.  Progress: a
+// block only ever spins on tickets lower than one it holds, and the block holding the lowest
+// unresolved ticket never spins.  The one partial tile (if any) is done by onesweep_tile<false>.
+// ---------------------------------------------------------------------------------------
 template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
@@ -574,38 +591,228 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 uint32_t* __restrict__ gprefix, uint32_t* __restrict__ ticket,
                 const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out)
 {
+    using ValT = typename ValueOf<VBYTES>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST>;
     static_assert((uint64_t)GROUP_TILES * SM::TILE < (1ull << GROUP_SUM_BITS), "group accumulator overflow");
+    static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit in the scan");
     constexpr int TILE = SM::TILE;
+    constexpr int WARPS = SM::WARPS;
+    constexpr bool PAIRS = VBYTES > 0;
+    constexpr bool PACKED = sizeof(KeyT) == 4 && VBYTES == 4;
+    constexpr int ROW = FAST ? RADIX : 2 * RADIX; // 32-bit words per warp row of the table
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t* s_misc = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN) + RADIX;
+    uint32_t* tbl32 = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_TBL);
+    uint2* s_kv = reinterpret_cast<uint2*>(smem_raw + SM::OFF_VAL);
+    ValT* s_vals = reinterpret_cast<ValT*>(smem_raw + SM::OFF_VAL);
+    KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw + SM::OFF_KEY);
+    uint32_t* s_off = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN);
+    uint32_t* s_misc = s_off + RADIX;
 
-    // ---- persistent blocks: tiles are handed out by an atomic ticket, so a tile only ever waits
-    // on tiles that already started (no deadlock whatever the block scheduler does)
-    if (threadIdx.x == 0) s_misc[15] = atomicAdd(ticket, 1u);
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+    uint32_t* tw32 = tbl32 + warp * ROW;
+    uint2* tw = reinterpret_cast<uint2*>(tw32);
+    auto mask_word = [](uint32_t d) { return 2u * d + ((d >> 4) & 1u); };
+    auto base_word = [](uint32_t d) { return FAST ? d : 2u * d + (((d >> 4) & 1u) ^ 1u); };
+    const uint32_t my0 = warp * (32 * ITEMS) + lane;
+
+    const uint32_t num_tiles = (n + TILE - 1) / TILE;
+    const uint32_t full_tiles = n / TILE;
+
+    if (tid == 0) s_misc[15] = atomicAdd(ticket, 1u);
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
-        for (int i = threadIdx.x; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = tid; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
     __syncthreads();
     uint32_t tile = s_misc[15];
-    const uint32_t num_tiles = (n + TILE - 1) / TILE;
     KeyT key[ITEMS];
     if (tile < num_tiles) {
         const size_t tb = (size_t)tile * TILE;
         load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, tb, (n - tb) < (size_t)TILE ? (uint32_t)(n - tb) : (uint32_t)TILE);
     }
-    while (tile < num_tiles) {
+
+    bool have_prev = false;
+    uint32_t p_tile = 0, p_count = 0, p_bin_start = 0;
+    uint32_t lb_v[GROUP_TILES - 1], lb_ga[GROUP_LOOK], lb_gq[GROUP_LOOK];
+    uint32_t iter = 0;
+    while (true) {
+        const bool cur = tile < full_tiles; // block-uniform
+        if (!cur && !have_prev) break;
         const size_t tile_base = (size_t)tile * TILE;
-        const uint32_t tile_valid = (n - tile_base) < (size_t)TILE ? (uint32_t)(n - tile_base) : (uint32_t)TILE;
-        if (tile_valid == (uint32_t)TILE)
-            tile = onesweep_tile<true, FAST, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
-                key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
-                base_out, tile, tile == num_tiles - 1, tile_base, tile_valid, smem_raw);
-        else
-            tile = onesweep_tile<false, FAST, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
-                key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
-                base_out, tile, tile == num_tiles - 1, tile_base, tile_valid, smem_raw);
+        uint32_t count = 0;
+        ValT val[PAIRS ? ITEMS : 1];
+        if (cur) {
+            // ticket of the tile after this one (slot alternates: it is read a full iteration later)
+            if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
+            // ---- phase A(tile): per-warp digit counts
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j) atomicAdd(tw32 + base_word(digit_of<KIND, DESC>(key[j], bit)), 1u);
+            if (PAIRS) {
+                const ValT* vin = vals_in + tile_base + my0;
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) val[j] = vin[j * 32];
+            }
+        }
+        __syncthreads();
+
+        // ---- scan(tile): thread d owns digit d
+        if (cur && tid < RADIX) {
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
+            st_relaxed(status + (size_t)tile * RADIX + tid, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+            atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
+        }
+        const uint32_t bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
+        if (cur && tid < RADIX) {
+            uint32_t run = bin_start;
+#pragma unroll
+            for (int w = 0; w < WARPS; ++w) {
+                uint32_t* cell = tbl32 + w * ROW + base_word(tid);
+                const uint32_t c = *cell;
+                *cell = run;
+                run += c;
+            }
+        }
+
+        // ---- resolve(prev): the look-back loads were issued at the end of the previous iteration
+        if (have_prev && tid < RADIX) {
+            uint32_t excl = 0;
+            if (p_tile != 0) {
+                const uint32_t g = p_tile / GROUP_TILES, r = p_tile % GROUP_TILES;
+                const uint32_t* col = status + tid;
+                const uint32_t* gs = gsum + tid;
+                uint32_t* gp = gprefix + tid;
+                bool done = false;
+#pragma unroll
+                for (int i = 0; i < GROUP_TILES - 1; ++i) {
+                    if ((uint32_t)i < r && !done) {
+                        uint32_t sv = lb_v[i];
+                        while ((sv >> FLAG_SHIFT) == 0u) sv = ld_relaxed(col + (size_t)(p_tile - 1 - i) * RADIX);
+                        excl += sv & VALUE_MASK;
+                        done = (sv >> FLAG_SHIFT) == 2u;
+                    }
+                }
+                if (!done) {
+                    // excl = counts of the group's earlier tiles; add the prefix through group g-1
+                    uint32_t pg = 0, gg = g;
+                    bool have = false;
+#pragma unroll
+                    for (int j = 0; j < GROUP_LOOK; ++j) {
+                        if (!have && gg == g - (uint32_t)j) {
+                            if ((lb_gq[j] >> FLAG_SHIFT) == 2u) { pg += lb_gq[j] & VALUE_MASK; have = true; }
+                            else if ((lb_ga[j] >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += lb_ga[j] & GROUP_SUM_MASK; --gg; }
+                        }
+                    }
+                    while (!have) { // beyond the prefetched rows, or a group still filling: poll
+                        const uint32_t q = gg == 0u ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
+                        if ((q >> FLAG_SHIFT) == 2u) { pg += q & VALUE_MASK; have = true; break; }
+                        const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
+                        if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
+                    }
+                    st_relaxed(gp + (size_t)g * RADIX, FLAG_PREFIX | pg);
+                    excl += pg;
+                }
+                st_relaxed(status + (size_t)p_tile * RADIX + tid, FLAG_PREFIX | (excl + p_count));
+            }
+            const uint32_t gbase = base_in[tid] + excl;
+            s_off[tid] = gbase - p_bin_start;
+            if (base_out != nullptr && p_tile == num_tiles - 1) base_out[tid] = gbase + p_count;
+        }
+        __syncthreads();
+
+        // ---- read-out(prev): consecutive threads take consecutive tile-sorted slots
+        if (have_prev) {
+#pragma unroll
+            for (int k = 0; k < ITEMS; ++k) {
+                const uint32_t p = k * THREADS + tid;
+                if (PACKED) {
+                    const uint2 kv = s_kv[p];
+                    const uint32_t dst = s_off[digit_of<KIND, DESC>((KeyT)kv.x, bit)] + p;
+                    keys_out[dst] = (KeyT)kv.x;
+                    store32(vals_out + dst, kv.y);
+                } else {
+                    const KeyT kk = s_keys[p];
+                    const uint32_t dst = s_off[digit_of<KIND, DESC>(kk, bit)] + p;
+                    keys_out[dst] = kk;
+                    if (PAIRS) vals_out[dst] = s_vals[p];
+                }
+            }
+        }
+        __syncthreads();
+        if (!cur) break;
+
+        // ---- phase C(tile): rank and stage at the tile-sorted position
+        const uint32_t next_tile = s_misc[12 + (iter & 1u)];
+        const uint32_t lane_bit = 1u << lane;
+        const uint32_t lane_lt = lane_bit - 1u;
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            // bit_c == bit (second kernel parameter): keeps ptxas from holding phase A's temporaries
+            const uint32_t d = digit_of<KIND, DESC>(key[j], bit_c);
+            uint32_t pos;
+            if (FAST) {
+                pos = atomicAdd(tw32 + d, 1u); // old value = stable position (probe.cuh)
+                __syncwarp();
+            } else {
+                const bool swapped = (d >> 4) & 1u;
+                atomicOr(tw32 + mask_word(d), lane_bit);
+                __syncwarp();
+                const uint2 raw = tw[d];
+                const uint2 e = swapped ? make_uint2(raw.y, raw.x) : raw;
+                const uint32_t lower = __popc(e.x & lane_lt);
+                __syncwarp();
+                if (lower == 0) {
+                    const uint32_t nb = e.y + __popc(e.x);
+                    tw[d] = swapped ? make_uint2(nb, 0u) : make_uint2(0u, nb);
+                }
+                __syncwarp();
+                pos = e.y + lower;
+            }
+            if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
+            else {
+                s_keys[pos] = key[j];
+                if (PAIRS) s_vals[pos] = val[j];
+            }
+        }
+        // this warp's table row is private until the next scan: zero it for the next phase A
+        __syncwarp();
+        {
+            uint4* z = reinterpret_cast<uint4*>(tw32);
+#pragma unroll
+            for (int i = lane; i < ROW / 4; i += 32) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        __syncwarp();
+
+        // ---- look-back loads of this tile (consumed next iteration), then the next tile's keys
+        if (tid < RADIX && tile != 0) {
+            const uint32_t g = tile / GROUP_TILES, r = tile % GROUP_TILES;
+#pragma unroll
+            for (int i = 0; i < GROUP_TILES - 1; ++i)
+                lb_v[i] = ((uint32_t)i < r) ? ld_relaxed(status + tid + (size_t)(tile - 1 - i) * RADIX) : 0u;
+#pragma unroll
+            for (int j = 0; j < GROUP_LOOK; ++j) {
+                const bool in = g >= (uint32_t)j + 1u; // group g-j has a predecessor group
+                lb_gq[j] = in ? ld_relaxed(gprefix + tid + (size_t)(g - j) * RADIX) : FLAG_PREFIX;
+                lb_ga[j] = in ? ld_relaxed(gsum + tid + (size_t)(g - j - 1) * RADIX) : 0u;
+            }
+        }
+        if (next_tile < num_tiles) {
+            const size_t nb = (size_t)next_tile * TILE;
+            load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, nb, (n - nb) < (size_t)TILE ? (uint32_t)(n - nb) : (uint32_t)TILE);
+        }
+        p_tile = tile; p_count = count; p_bin_start = bin_start; have_prev = true;
+        tile = next_tile;
+        ++iter;
+    }
+
+    // ---- the partial last tile, if this block drew its ticket (straight-line path)
+    if (tile == full_tiles && full_tiles < num_tiles) {
+        const size_t tile_base = (size_t)tile * TILE;
+        onesweep_tile<false, FAST, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
+            key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
+            base_out, tile, true, tile_base, (uint32_t)(n - tile_base), smem_raw);
     }
 }
 

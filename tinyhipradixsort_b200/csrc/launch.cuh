@@ -12,11 +12,19 @@ namespace thrs_b200 {
 // table cells), otherwise match-mask ranking (8-byte cells).
 #ifndef THRS_TUNE_THREADS
 #define THRS_TUNE_THREADS 256
-#define THRS_TUNE_ITEMS 28
-#define THRS_TUNE_MINB 3
+#define THRS_TUNE_ITEMS 40
+#define THRS_TUNE_MINB 2
+#endif
+#ifndef THRS_TUNE_K_THREADS // keys-only shape
+#define THRS_TUNE_K_THREADS 256
+#define THRS_TUNE_K_ITEMS 40
+#define THRS_TUNE_K_MINB 3
 #endif
 template <int KBYTES, int VBYTES, bool FAST> struct Tuning {
     static constexpr int THREADS = THRS_TUNE_THREADS, ITEMS = THRS_TUNE_ITEMS, MINB = THRS_TUNE_MINB;
+};
+template <bool FAST> struct Tuning<4, 0, FAST> {
+    static constexpr int THREADS = THRS_TUNE_K_THREADS, ITEMS = THRS_TUNE_K_ITEMS, MINB = THRS_TUNE_K_MINB;
 };
 template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
 template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
