@@ -17,8 +17,8 @@ namespace thrs_b200 {
 #endif
 #ifndef THRS_TUNE_K_THREADS // keys-only shape
 #define THRS_TUNE_K_THREADS 256
-#define THRS_TUNE_K_ITEMS 40
-#define THRS_TUNE_K_MINB 3
+#define THRS_TUNE_K_ITEMS 64
+#define THRS_TUNE_K_MINB 2
 #endif
 template <int KBYTES, int VBYTES, bool FAST> struct Tuning {
     static constexpr int THREADS = THRS_TUNE_THREADS, ITEMS = THRS_TUNE_ITEMS, MINB = THRS_TUNE_MINB;
