@@ -424,6 +424,7 @@ int thrs_set_ranking(thrs_sorter* s, int ranking)
     if (ranking < THRS_RANKING_AUTO || ranking > THRS_RANKING_COUNTER_RETURN)
         return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_ranking: bad ranking");
     s->ranking_request = ranking;
+    s->fast = (ranking == THRS_RANKING_MATCH_MASK) ? 0 : (ranking == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
     return THRS_OK;
 }
 
@@ -434,6 +435,7 @@ int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in_order, u
     if (rc) return rc;
     const int fast = (s->ranking_request == THRS_RANKING_MATCH_MASK) ? 0
                      : (s->ranking_request == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
+    s->fast = fast;
     if (ranking_in_use) *ranking_in_use = fast ? THRS_RANKING_COUNTER_RETURN : THRS_RANKING_MATCH_MASK;
     if (probe_in_order) *probe_in_order = s->probe_in_order;
     if (probe_groups) *probe_groups = s->probe_groups;
