@@ -79,6 +79,36 @@ def ref_perf(n=1 << 28):
           f"=> {n / min(ts) / 1e6:.2f} Gkeys/s", flush=True)
 
 
+def perf_types(log2n=26):
+    """Per-pass time of the other key/value instantiations on uniform random keys."""
+    n = 1 << log2n
+    g = torch.Generator(device="cuda"); g.manual_seed(1)
+    for key, vb in (("u32", 8), ("u32", 16), ("u64", None), ("u64", 4), ("u64", 8), ("f64", 16), ("f32", 4)):
+        kb = 4 if key in ("u32", "f32") else 8
+        k0 = torch.randint(-2**31, 2**31 - 1, (n * kb // 4,), dtype=torch.int32, device="cuda", generator=g)
+        v0 = torch.zeros(n * (vb or 4) // 4, dtype=torch.int32, device="cuda")
+        s = make_sorter(key, vb)
+        d = s.getTemporaryBufferBytes(n)
+        tmp = torch.empty(d.getTemporaryBufferBytesForSortPairs() if vb else d.getTemporaryBufferBytesForSortKeys(),
+                          dtype=torch.uint8, device="cuda")
+        s.profile(True)
+        k, v = k0.clone(), v0.clone()
+        best = None
+        for r in range(5):
+            k.copy_(k0); v.copy_(v0)
+            if vb:
+                s.sortPairs(k, v, n, tmp, 0, kb * 8)
+            else:
+                s.sortKeys(k, n, tmp, 0, kb * 8)
+            p = s.readProfile()
+            if r >= 1 and (best is None or p["total_ms"] < best["total_ms"]):
+                best = p
+        per_pass = sum(best["pass_ms"]) / len(best["pass_ms"])
+        gbs = 2 * n * (kb + (vb or 0)) / per_pass / 1e6
+        print(f"{key}+{vb}: n=2^{log2n} total {best['total_ms']:.3f} ms, {per_pass:.3f} ms/pass = {gbs:.0f} GB/s per pass, "
+              f"{n / best['total_ms'] / 1e6:.2f} Gkeys/s (tile {s.tileItems()})", flush=True)
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["parity", "perf", "ref"]
     print(torch.cuda.get_device_name(0), flush=True)
@@ -88,5 +118,7 @@ if __name__ == "__main__":
         perf(1 << 28, True)
         perf(1 << 28, False)
         perf(1 << 20, False)
+    if "types" in what:
+        perf_types()
     if "ref" in what:
         ref_perf()

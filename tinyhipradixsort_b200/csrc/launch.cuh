@@ -26,12 +26,22 @@ template <int KBYTES, int VBYTES, bool FAST> struct Tuning {
 template <bool FAST> struct Tuning<4, 0, FAST> {
     static constexpr int THREADS = THRS_TUNE_K_THREADS, ITEMS = THRS_TUNE_K_ITEMS, MINB = THRS_TUNE_K_MINB;
 };
+#ifndef THRS_TUNE_OLD_SHAPES
+// bytes staged per item = K + V; two blocks of 256 threads per SM within 227 KiB and 128 registers
+template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 256, ITEMS = 32, MINB = 2; };
+template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 256, ITEMS = 20, MINB = 2; };
+template <bool FAST> struct Tuning<8, 0, FAST> { static constexpr int THREADS = 256, ITEMS = 40, MINB = 2; };
+template <bool FAST> struct Tuning<8, 4, FAST> { static constexpr int THREADS = 256, ITEMS = 32, MINB = 2; };
+template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 256, ITEMS = 24, MINB = 2; };
+template <bool FAST> struct Tuning<8, 16, FAST> { static constexpr int THREADS = 256, ITEMS = 16, MINB = 2; };
+#else
 template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
 template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
 template <bool FAST> struct Tuning<8, 0, FAST> { static constexpr int THREADS = 512, ITEMS = 12, MINB = 2; };
 template <bool FAST> struct Tuning<8, 4, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
 template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
 template <bool FAST> struct Tuning<8, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
+#endif
 
 struct OnesweepArgs {
     const void* keys_in;
