@@ -145,6 +145,22 @@ typedef struct thrs_profile {
 THRS_API int thrs_profile_enable(thrs_sorter* s, int on);
 THRS_API int thrs_profile_read(thrs_sorter* s, thrs_profile* out);
 
+/* Multi-GPU layer (no counterpart in the reference, single device: unittest.cpp:22,51).
+ * thrs_scatter_pairs: ONE stable 8-bit pass at start_bit whose output is not one array but 256
+ * runs: the item with digit d (in sort order, i.e. of getKeyBits ^ order mask) that is the r-th
+ * such item of the input goes to ((K*)key_dst[d])[first_index[d] + r], its value likewise through
+ * val_dst.  key_dst/val_dst/first_index are HOST arrays of 256 entries holding device addresses
+ * (they may point into other GPUs' memory opened with thrs_ipc_open: the pass then IS the
+ * exchange over NVLink).  4- and 8-byte values; n < 2^30; temp as for thrs_sort_pairs.
+ * thrs_ipc_*: cudaIpcGetMemHandle / OpenMemHandle / CloseMemHandle for one-process-per-GPU hosts;
+ * the 64-byte handle travels through the host's own channel (torch.distributed here). */
+THRS_API int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uint32_t n, void* temp,
+                                int start_bit, const uint64_t* key_dst, const uint64_t* val_dst,
+                                const uint32_t* first_index, void* stream);
+THRS_API int thrs_ipc_export(void* device_ptr, void* handle64);
+THRS_API int thrs_ipc_open(const void* handle64, void** out_device_ptr);
+THRS_API int thrs_ipc_close(void* device_ptr);
+
 /* Ranking used by the onesweep kernels (no counterpart in the reference, which has one scheme,
  * kernel.cu:293-345).  COUNTER_RETURN takes the old value of a returning shared-memory atomicAdd
  * as the stable rank; it is exact only where lanes that hit one counter in one warp instruction

@@ -67,6 +67,12 @@ SIGNATURES = {
     "thrs_version": (ctypes.c_char_p, []),
     "thrs_last_launch_count": (ctypes.c_int, []),
     "thrs_tile_items": (ctypes.c_uint32, [ctypes.c_void_p]),
+    "thrs_scatter_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
+                                          ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                          ctypes.c_void_p, ctypes.c_void_p]),
+    "thrs_ipc_export": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "thrs_ipc_open": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "thrs_ipc_close": (ctypes.c_int, [ctypes.c_void_p]),
     "thrs_set_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_get_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),
                                         ctypes.POINTER(ctypes.c_uint64)]),

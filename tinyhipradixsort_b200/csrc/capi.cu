@@ -159,7 +159,10 @@ static int prepare_device(thrs_sorter* s)
         cudaError_t e = cudaGetDevice(&dev);
         if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, dev);
         for (int f = 0; f < 2; ++f)
-            for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare[f][v]();
+            for (int v = 0; v < 4 && e == cudaSuccess; ++v) {
+                e = s->table->prepare[f][v]();
+                if (e == cudaSuccess && s->table->prepare_scatter[f][v]) e = s->table->prepare_scatter[f][v]();
+            }
         if (e == cudaSuccess) e = s->table->prepare_histogram();
         // which ranking this device can run exactly (probe.cuh); once per process and device
         if (e == cudaSuccess) {
@@ -331,6 +334,83 @@ int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, int start
         CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bit, 1, sc, (int)grid, stream), "histogram_kernel launch");
     }
     CUDA_TRY(cudaMemcpyAsync(counts_out, sc.hist(), 4ull * RADIX, cudaMemcpyDeviceToDevice, stream), "copy histogram");
+    return THRS_OK;
+}
+
+int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uint32_t n, void* temp, int start_bit,
+                       const uint64_t* key_dst, const uint64_t* val_dst, const uint32_t* first_index, void* stream_)
+{
+    g_launches = 0;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (!s || !temp || !key_dst || !val_dst || !first_index || ((!keys || !values) && n))
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: NULL argument");
+    if (start_bit < 0 || start_bit >= s->kbytes * 8) return fail(THRS_ERR_BIT_RANGE, "thrs_scatter_pairs: start_bit outside the key");
+    if (n == 0) return THRS_OK;
+    int rc = prepare_device(s);
+    if (rc) return rc;
+    s->fast = (s->ranking_request == THRS_RANKING_MATCH_MASK) ? 0
+              : (s->ranking_request == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
+    if (!s->table->scatter[s->fast][s->vslot])
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: 4- and 8-byte values only");
+    const uint32_t tile = s->table->tile_items[s->fast][s->vslot];
+    const uint64_t tiles_total = div_up(n, tile);
+    const uint64_t part_items = (uint64_t)(VALUE_MASK / tile) * tile;
+    if (n > part_items) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: n must stay below 2^30");
+    Scratch sc{static_cast<uint32_t*>(temp)};
+    // control block + the status rows of "pass 0"; the three tables live where pass 1 would
+    CUDA_TRY(cudaMemsetAsync(temp, 0, 4ull * (Scratch::CONTROL_WORDS + Scratch::pass_words(tiles_total)), stream),
+             "cudaMemsetAsync(scratch)");
+    uint32_t* tables = sc.status(1, tiles_total);
+    uint32_t* d_first = tables;
+    unsigned long long* d_kdst = reinterpret_cast<unsigned long long*>(tables + RADIX);
+    unsigned long long* d_vdst = d_kdst + RADIX;
+    CUDA_TRY(cudaMemcpyAsync(d_first, first_index, 4ull * RADIX, cudaMemcpyHostToDevice, stream), "upload first_index");
+    CUDA_TRY(cudaMemcpyAsync(d_kdst, key_dst, 8ull * RADIX, cudaMemcpyHostToDevice, stream), "upload key_dst");
+    CUDA_TRY(cudaMemcpyAsync(d_vdst, val_dst, 8ull * RADIX, cudaMemcpyHostToDevice, stream), "upload val_dst");
+    OnesweepArgs a;
+    a.keys_in = keys;
+    a.keys_out = nullptr;
+    a.vals_in = values;
+    a.vals_out = nullptr;
+    a.n = n;
+    a.bit = (uint32_t)start_bit;
+    a.status = sc.status(0, tiles_total);
+    a.gsum = sc.gsum(0, tiles_total);
+    a.gprefix = sc.gprefix(0, tiles_total);
+    a.ticket = sc.ticket(0, 0);
+    a.sm_count = s->sm_count;
+    a.base_in = d_first;
+    a.base_out = nullptr;
+    a.peer_keys = d_kdst;
+    a.peer_vals = d_vdst;
+    CUDA_TRY(s->table->scatter[s->fast][s->vslot](a, stream), "onesweep_kernel (scatter) launch");
+    ++g_launches;
+    return THRS_OK;
+}
+
+int thrs_ipc_export(void* device_ptr, void* handle64)
+{
+    if (!device_ptr || !handle64) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_ipc_export: NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size is part of the ABI");
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, device_ptr), "cudaIpcGetMemHandle");
+    memcpy(handle64, &h, 64);
+    return THRS_OK;
+}
+
+int thrs_ipc_open(const void* handle64, void** out_device_ptr)
+{
+    if (!handle64 || !out_device_ptr) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_ipc_open: NULL argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    CUDA_TRY(cudaIpcOpenMemHandle(out_device_ptr, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle");
+    return THRS_OK;
+}
+
+int thrs_ipc_close(void* device_ptr)
+{
+    if (!device_ptr) return THRS_OK;
+    CUDA_TRY(cudaIpcCloseMemHandle(device_ptr), "cudaIpcCloseMemHandle");
     return THRS_OK;
 }
 

@@ -289,7 +289,8 @@ template <> struct ValueOf<16> { using type = uint4; };
 
 // FAST selects the counter-return ranking (one 32-bit counter per warp and digit) instead of the
 // match-mask ranking ({mask, base} pairs); see onesweep_tile.
-template <class KeyT, int VBYTES, int THREADS, int ITEMS, bool FAST>
+// PEER adds two tables of 256 destination pointers (scatter pass of the multi-GPU layer).
+template <class KeyT, int VBYTES, int THREADS, int ITEMS, bool FAST, bool PEER = false>
 struct OnesweepSmem {
     static constexpr int WARPS = THREADS / 32;
     static constexpr int TILE = THREADS * ITEMS;
@@ -300,7 +301,8 @@ struct OnesweepSmem {
     static constexpr size_t OFF_VAL = OFF_TBL + TBL_BYTES; // 16-byte aligned (uint4 values)
     static constexpr size_t OFF_KEY = OFF_VAL + VAL_BYTES;
     static constexpr size_t OFF_BIN = OFF_KEY + KEY_BYTES;
-    static constexpr size_t BYTES = OFF_BIN + RADIX * 4 + 64;
+    static constexpr size_t OFF_PTR = OFF_BIN + RADIX * 4 + 64; // 8-byte aligned
+    static constexpr size_t BYTES = OFF_PTR + (PEER ? 2 * RADIX * 8 : 0);
 };
 
 // Keys of one tile into registers, warp-striped.  `valid` == TILE takes the unguarded path.
@@ -322,7 +324,7 @@ __device__ __forceinline__ void load_tile_keys(KeyT (&key)[ITEMS], const KeyT* _
 // One tile.  `key` holds the tile's keys on entry and the NEXT tile's keys on return (they are
 // requested as soon as this tile's keys are staged, so their latency and the ticket's hide behind
 // the look-back and the read-out).  Returns the next tile's ticket.
-template <bool FULL, bool FAST, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
+template <bool FULL, bool FAST, bool PEER, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
 __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT* __restrict__ keys_in, uint32_t n,
                                               uint32_t num_tiles, uint32_t* __restrict__ ticket,
                                               KeyT* __restrict__ keys_out,
@@ -334,7 +336,9 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                                               size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw)
 {
     using ValT = typename ValueOf<VBYTES>::type;
-    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST>;
+    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST, PEER>;
+    const unsigned long long* s_kptr = reinterpret_cast<const unsigned long long*>(smem_raw + SM::OFF_PTR);
+    const unsigned long long* s_vptr = s_kptr + RADIX;
     constexpr int WARPS = SM::WARPS;
     constexpr bool PAIRS = VBYTES > 0;
     // 4-byte key + 4-byte value travel through shared memory as one 8-byte element: a random
@@ -543,14 +547,22 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         if (FULL || p < tile_valid) {
             if (PACKED) {
                 const uint2 kv = s_kv[p];
-                const uint32_t dst = s_off[digit_of<KIND, DESC>((KeyT)kv.x, bit)] + p;
-                keys_out[dst] = (KeyT)kv.x;
-                store32(vals_out + dst, kv.y);
+                const uint32_t d = digit_of<KIND, DESC>((KeyT)kv.x, bit);
+                const uint32_t dst = s_off[d] + p;
+                KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
+                ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
+                ko[dst] = (KeyT)kv.x;
+                store32(vo + dst, kv.y);
             } else {
                 const KeyT kk = s_keys[p];
-                const uint32_t dst = s_off[digit_of<KIND, DESC>(kk, bit)] + p;
-                keys_out[dst] = kk;
-                if (PAIRS) vals_out[dst] = s_vals[p];
+                const uint32_t d = digit_of<KIND, DESC>(kk, bit);
+                const uint32_t dst = s_off[d] + p;
+                KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
+                ko[dst] = kk;
+                if (PAIRS) {
+                    ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
+                    vo[dst] = s_vals[p];
+                }
             }
         }
     }
@@ -582,17 +594,21 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 // block only ever spins on tickets lower than one it holds, and the block holding the lowest
 // unresolved ticket never spins.  The one partial tile (if any) is done by onesweep_tile<false>.
 // ---------------------------------------------------------------------------------------
-template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST>
+// PEER: the scatter pass of the multi-GPU layer.  Digit d's run goes to peer_keys[d] / peer_vals[d]
+// (device arrays of 256 pointers, possibly into other GPUs' memory over NVLink) at element
+// base_in[d] + rank; keys_out / vals_out are unused.
+template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST, bool PEER>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
                 typename ValueOf<VBYTES>::type* __restrict__ vals_out,
                 uint32_t n, uint32_t bit, uint32_t bit_c, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
                 uint32_t* __restrict__ gprefix, uint32_t* __restrict__ ticket,
-                const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out)
+                const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out,
+                const unsigned long long* __restrict__ peer_keys, const unsigned long long* __restrict__ peer_vals)
 {
     using ValT = typename ValueOf<VBYTES>::type;
-    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST>;
+    using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST, PEER>;
     static_assert((uint64_t)GROUP_TILES * SM::TILE < (1ull << GROUP_SUM_BITS), "group accumulator overflow");
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit in the scan");
     constexpr int TILE = SM::TILE;
@@ -607,10 +623,16 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw + SM::OFF_KEY);
     uint32_t* s_off = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN);
     uint32_t* s_misc = s_off + RADIX;
+    unsigned long long* s_kptr = reinterpret_cast<unsigned long long*>(smem_raw + SM::OFF_PTR);
+    unsigned long long* s_vptr = s_kptr + RADIX;
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
+    if (PEER && tid < RADIX) { // visible after the first barrier below
+        s_kptr[tid] = peer_keys[tid];
+        s_vptr[tid] = PAIRS ? peer_vals[tid] : 0ull;
+    }
     uint32_t* tw32 = tbl32 + warp * ROW;
     uint2* tw = reinterpret_cast<uint2*>(tw32);
     auto mask_word = [](uint32_t d) { return 2u * d + ((d >> 4) & 1u); };
@@ -729,14 +751,22 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const uint32_t p = k * THREADS + tid;
                 if (PACKED) {
                     const uint2 kv = s_kv[p];
-                    const uint32_t dst = s_off[digit_of<KIND, DESC>((KeyT)kv.x, bit)] + p;
-                    keys_out[dst] = (KeyT)kv.x;
-                    store32(vals_out + dst, kv.y);
+                    const uint32_t d = digit_of<KIND, DESC>((KeyT)kv.x, bit);
+                    const uint32_t dst = s_off[d] + p;
+                    KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
+                    ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
+                    ko[dst] = (KeyT)kv.x;
+                    store32(vo + dst, kv.y);
                 } else {
                     const KeyT kk = s_keys[p];
-                    const uint32_t dst = s_off[digit_of<KIND, DESC>(kk, bit)] + p;
-                    keys_out[dst] = kk;
-                    if (PAIRS) vals_out[dst] = s_vals[p];
+                    const uint32_t d = digit_of<KIND, DESC>(kk, bit);
+                    const uint32_t dst = s_off[d] + p;
+                    KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
+                    ko[dst] = kk;
+                    if (PAIRS) {
+                        ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
+                        vo[dst] = s_vals[p];
+                    }
                 }
             }
         }
@@ -810,7 +840,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     // ---- the partial last tile, if this block drew its ticket (straight-line path)
     if (tile == full_tiles && full_tiles < num_tiles) {
         const size_t tile_base = (size_t)tile * TILE;
-        onesweep_tile<false, FAST, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
+        onesweep_tile<false, FAST, PEER, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
             key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
             base_out, tile, true, tile_base, (uint32_t)(n - tile_base), smem_raw);
     }

@@ -57,6 +57,9 @@ struct OnesweepArgs {
     int sm_count;
     const uint32_t* base_in;
     uint32_t* base_out;
+    // scatter pass only: device arrays of 256 destination pointers (keys / values per digit)
+    const unsigned long long* peer_keys = nullptr;
+    const unsigned long long* peer_vals = nullptr;
 };
 
 struct KernelTable {
@@ -68,6 +71,9 @@ struct KernelTable {
     cudaError_t (*prepare[2][4])(); // opt in to > 48 KiB dynamic shared memory
     cudaError_t (*prepare_histogram)();
     uint32_t tile_items[2][4];
+    // scatter pass (per-digit destination pointers); 4- and 8-byte values only, else nullptr
+    cudaError_t (*scatter[2][4])(const OnesweepArgs& a, cudaStream_t stream);
+    cudaError_t (*prepare_scatter[2][4])();
 };
 
 template <class KeyT, int KIND, bool DESC, int PASSES>
@@ -123,28 +129,29 @@ cudaError_t prepare_histogram()
     return e;
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false>
 cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
 {
     using T = Tuning<(int)sizeof(KeyT), VBYTES, FAST>;
-    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST>;
+    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
     using ValT = typename ValueOf<VBYTES>::type;
     const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
     // persistent blocks, T::MINB per SM; correctness does not depend on all of them being resident
     const uint32_t cap = (uint32_t)a.sm_count * T::MINB;
     const uint32_t grid = tiles < cap ? tiles : cap;
-    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST><<<grid, T::THREADS, SM::BYTES, stream>>>(
+    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER><<<grid, T::THREADS, SM::BYTES, stream>>>(
         static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
-        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out);
+        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out,
+        a.peer_keys, a.peer_vals);
     return cudaGetLastError();
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false>
 cudaError_t prepare_onesweep()
 {
     using T = Tuning<(int)sizeof(KeyT), VBYTES, FAST>;
-    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST>;
-    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST>,
+    using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
+    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES);
 }
 
@@ -166,7 +173,11 @@ const KernelTable* make_table()
           &prepare_onesweep<KeyT, KIND, DESC, 8, true>, &prepare_onesweep<KeyT, KIND, DESC, 16, true>}},
         &prepare_histogram<KeyT, KIND, DESC>,
         {{tile_of<KB, 0, false>(), tile_of<KB, 4, false>(), tile_of<KB, 8, false>(), tile_of<KB, 16, false>()},
-         {tile_of<KB, 0, true>(), tile_of<KB, 4, true>(), tile_of<KB, 8, true>(), tile_of<KB, 16, true>()}}};
+         {tile_of<KB, 0, true>(), tile_of<KB, 4, true>(), tile_of<KB, 8, true>(), tile_of<KB, 16, true>()}},
+        {{nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, false, true>, &launch_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},
+         {nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, true, true>, &launch_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}},
+        {{nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},
+         {nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, true, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}}};
     return &t;
 }
 

@@ -11,7 +11,11 @@ SURVEY.md 8(e):
      equal keys never straddle ranks and the destination is monotone in the digit;
   4. one stable onesweep pass on the top digit (thrs_sort_pairs on bits [top-8, top)) groups the
      slice by destination without reordering anything inside a bucket;
-  5. key and value all-to-all(v) over NVLink (NCCL send/recv): chunks land in SOURCE-RANK order;
+  5. exchange; chunks land in SOURCE-RANK order.  On GPUs steps 4+5 are ONE kernel: the pass of
+     step 4 stores every digit run straight into its destination rank's receive buffer over
+     NVLink (thrs_scatter_pairs with CUDA-IPC peer pointers, `scatter_exchange`), followed by a
+     one-word all_reduce as the "everyone has written" barrier.  Hosts without peer memory (the
+     gloo CPU tests) run step 4 locally and then an all_to_all_single per array;
   6. local 4-pass onesweep over what was received.
 
 Concatenating the ranks' outputs gives exactly std::stable_sort of the concatenated inputs:
@@ -43,6 +47,20 @@ def plan_partition(all_hists, world):
     for d in range(world):
         send[:, d] = h[:, dest == d].sum(axis=1)
     return dest, send
+
+
+def scatter_tables(all_hists, dest, send, me):
+    """Where rank `me`'s run of digit d starts inside its destination's receive buffer (elements):
+    chunks are laid out in source-rank order, digits ascending inside a chunk."""
+    h = np.asarray(all_hists, dtype=np.int64).reshape(-1, 256)
+    first = np.zeros(256, dtype=np.int64)
+    world = send.shape[0]
+    for r in range(world):
+        start = int(send[:me, r].sum())
+        for d in np.nonzero(dest == r)[0]:
+            first[d] = start
+            start += int(h[me, d])
+    return first
 
 
 class CudaLocalOps:
@@ -83,6 +101,55 @@ class CudaLocalOps:
     def launches(self):
         return self.sorter.lastLaunchCount()
 
+    # ---- peer-memory exchange (one process per GPU, CUDA IPC) ----
+    def exchange_alloc(self, cap_items, kbytes, vbytes):
+        """cudaMalloc'ed receive buffer [keys cap | values cap] and its IPC handle."""
+        from .radixsort import Buffer, ipc_export
+
+        self._xcap = int(cap_items)
+        self._xkoff = 0
+        self._xvoff = (self._xcap * kbytes + 255) & ~255
+        self._xbuf = Buffer(self._xvoff + self._xcap * vbytes)
+        return ipc_export(self._xbuf.data())
+
+    def exchange_open(self, handles, me):
+        """Device addresses of every rank's receive buffer in this process (own one included)."""
+        from .radixsort import ipc_close, ipc_open
+
+        for p in getattr(self, "_xpeers_opened", []):
+            ipc_close(p)
+        self._xpeers_opened = []
+        bases = []
+        for r, h in enumerate(handles):
+            if r == me:
+                bases.append(self._xbuf.data())
+            else:
+                p = ipc_open(h)
+                self._xpeers_opened.append(p)
+                bases.append(p)
+        self._xbases = bases
+        return bases
+
+    def exchange_views(self, count, key_dtype, val_dtype):
+        """torch views of the first `count` received keys / values."""
+        torch = self.torch
+
+        class _Raw:
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+        ts = {torch.int32: "<i4", torch.int64: "<i8"}
+        k = torch.as_tensor(_Raw(self._xbuf.data() + self._xkoff, max(count, 1), ts[key_dtype]), device="cuda")
+        v = torch.as_tensor(_Raw(self._xbuf.data() + self._xvoff, max(count, 1), ts[val_dtype]), device="cuda")
+        return k[:count], v[:count]
+
+    def scatter_exchange(self, keys, vals, n, start_bit, dest, first):
+        """Steps 4+5 fused: digit d's run -> receive buffer of rank dest[d] at element first[d]."""
+        kd = np.array([self._xbases[int(r)] + self._xkoff for r in dest], dtype=np.uint64)
+        vd = np.array([self._xbases[int(r)] + self._xvoff for r in dest], dtype=np.uint64)
+        if n:
+            self.sorter.scatterPairs(keys, vals, n, self._temp(n), start_bit, kd, vd, first.astype(np.uint32))
+
 
 class DistributedRadixSort:
     """sort_pairs(keys, values) over all ranks of `group`.  Returns (keys_out, values_out, count):
@@ -97,6 +164,8 @@ class DistributedRadixSort:
         self.rank = dist.get_rank(group)
         self.last_plan = None
         self._recv = None
+        self._xcap = 0
+        self.fused = hasattr(local_ops, "scatter_exchange")
 
     def _recv_buffers(self, like_k, like_v, count):
         import torch
@@ -133,6 +202,8 @@ class DistributedRadixSort:
         total_recv = sum(recv_counts)
         if total_recv >= 1 << 32:
             raise ValueError("a rank's share must stay below 2^32 items")
+        if self.fused:
+            return self._fused_exchange_and_sort(keys, vals, n, bits, all_h, dest, send, total_recv, mark)
         # 4: stable pass on the top digit = stable partition by destination
         ops.sort_pairs(keys, vals, n, bits - 8, bits)
         mark("partition pass")
@@ -142,6 +213,36 @@ class DistributedRadixSort:
         dist.all_to_all_single(rk, keys[:n], recv_counts, send_counts, group=self.group)
         dist.all_to_all_single(rv, vals[:n], recv_counts, send_counts, group=self.group)
         mark("all-to-all")
+        # 6: local sort of the received share
+        ops.sort_pairs(rk, rv, total_recv, 0, bits)
+        mark("local sort")
+        return rk, rv, total_recv
+
+
+    def _fused_exchange_and_sort(self, keys, vals, n, bits, all_h, dest, send, total_recv, mark):
+        import torch
+
+        dist, ops, P = self.dist, self.ops, self.world
+        # receive buffers: same capacity on every rank (a pure function of the shared send matrix),
+        # re-exported only when they have to grow
+        need = int(send.sum(axis=0).max())
+        if need > self._xcap:
+            cap = int(need * 1.02) + 1024
+            kb, vb = keys.element_size(), vals.element_size() * int(np.prod(vals.shape[1:], dtype=np.int64))
+            torch.cuda.synchronize()
+            handle = ops.exchange_alloc(cap, kb, vb)
+            handles = [None] * P
+            dist.all_gather_object(handles, handle, group=self.group)
+            ops.exchange_open(handles, self.rank)
+            self._xcap = cap
+        first = scatter_tables(all_h, dest, send, self.rank)
+        # 4+5: the partition pass stores straight into the destination ranks' receive buffers
+        ops.scatter_exchange(keys, vals, n, bits - 8, dest, first)
+        # "everyone has written": a one-word all_reduce ordered after the scatter kernel on every rank
+        flag = torch.ones(1, dtype=torch.int32, device=keys.device)
+        dist.all_reduce(flag, group=self.group)
+        mark("partition+exchange (peer stores)")
+        rk, rv = ops.exchange_views(total_recv, keys.dtype, vals.dtype)
         # 6: local sort of the received share
         ops.sort_pairs(rk, rv, total_recv, 0, bits)
         mark("local sort")
@@ -254,7 +355,7 @@ def bench(args, dist, rank, world, dev, g):
     ds.sort_pairs(keys, vals)
     prof = ops.sorter.readProfile()
     ops.sorter.profile(False)
-    launches_per_step = 1 + 2 + 5  # top-digit histogram, partition (histogram + 1 pass), local sort (histogram + 4)
+    launches_per_step = 1 + 1 + 5  # top-digit histogram, scatter pass, local sort (histogram + 4)
 
     # end to end: pinned host slices in, sorted share out (H2D + sort + D2H inside the timed region)
     hk0, hv0 = keys0.cpu().pin_memory(), vals0.cpu().pin_memory()
@@ -283,17 +384,19 @@ def bench(args, dist, rank, world, dev, g):
         avg_pass = sum(prof["pass_ms"]) / len(prof["pass_ms"])
         achieved = per_gpu_bytes / (avg_pass * 1e-3) / 1e9
         send_bytes = n_l * 8 * (world - 1) / world
-        a2a_ms = stage_sum.get("all-to-all", 0.0) / args.steps
+        fused = "partition+exchange (peer stores)" in stage_sum
+        a2a_ms = stage_sum.get("partition+exchange (peer stores)" if fused else "all-to-all", 0.0) / args.steps
         line = {
             "metric": g["METRIC"], "value": value, "unit": g["UNIT"], "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": f"C5 shape: {world} x 2^{args.log2n_per_gpu} uniform-random u32 key + u32 value pairs, "
-                                   "MSD splitters + NVLink all-to-all + local onesweep, stable, bits [0,32)",
+                                   "MSD splitters + partition pass storing into peer memory over NVLink + local onesweep, stable, bits [0,32)",
                        "n_total": total, "n_per_gpu": n_l, "parallelism": f"partitioned sort over {world} ranks (NCCL)",
                        "l2": "per-GPU inputs (>= 2 GiB) are larger than L2; input restored outside the timed events",
                        "stage_ms_rank0": {k: v / args.steps for k, v in stage_sum.items()},
-                       "all_to_all": {"bytes_sent_per_gpu": send_bytes, "ms": a2a_ms,
+                       "all_to_all": {"how": "fused into the partition kernel (P2P stores, CUDA IPC)" if fused else "NCCL all_to_all_single",
+                                      "bytes_sent_per_gpu": send_bytes, "ms": a2a_ms,
                                       "GBps_per_direction_per_gpu": (send_bytes / (a2a_ms * 1e-3) / 1e9) if a2a_ms else None,
                                       "nvlink_peak_GBps": 900.0}},
             "verified": verified,

@@ -97,6 +97,24 @@ def _stream(stream):
     return stream.cuda_stream
 
 
+def ipc_export(device_ptr):
+    """64-byte CUDA IPC handle of a cudaMalloc'ed allocation (thrs_ipc_export)."""
+    h = ctypes.create_string_buffer(64)
+    _check(_lib.load().thrs_ipc_export(_ptr(device_ptr), h))
+    return h.raw
+
+
+def ipc_open(handle):
+    """Map another process's allocation into this one (thrs_ipc_open); returns the device address."""
+    p = ctypes.c_void_p(0)
+    _check(_lib.load().thrs_ipc_open(ctypes.create_string_buffer(bytes(handle), 64), ctypes.byref(p)))
+    return int(p.value)
+
+
+def ipc_close(device_ptr):
+    _check(_lib.load().thrs_ipc_close(int(device_ptr)))
+
+
 class Buffer:
     """thrs::Buffer (hpp:501-528): RAII device allocation of max(bytes, 1), non-copyable."""
 
@@ -235,6 +253,21 @@ class RadixSort:
         return {"memset_ms": p.memset_ms, "histogram_ms": p.histogram_ms,
                 "pass_ms": [p.pass_ms[i] for i in range(p.passes)], "copyback_ms": p.copyback_ms,
                 "total_ms": p.total_ms, "passes": p.passes, "parts": p.parts}
+
+    def scatterPairs(self, inputKeyBuffer, inputValueBuffer, numberOfInputs, temporaryBuffer, startBit, keyDst, valDst,
+                     firstIndex, stream=None):
+        """One stable 8-bit pass whose 256 runs go to per-digit destinations (thrs_scatter_pairs):
+        keyDst / valDst are 256 device addresses (own or peer memory), firstIndex 256 element offsets."""
+        import numpy as np
+
+        kd = np.ascontiguousarray(keyDst, dtype=np.uint64)
+        vd = np.ascontiguousarray(valDst, dtype=np.uint64)
+        fi = np.ascontiguousarray(firstIndex, dtype=np.uint32)
+        if kd.shape != (256,) or vd.shape != (256,) or fi.shape != (256,):
+            raise ThrsError(1, "scatterPairs: the three tables have 256 entries")
+        _check(self._lib.thrs_scatter_pairs(self._h, _ptr(inputKeyBuffer), _ptr(inputValueBuffer), int(numberOfInputs),
+                                            _ptr(temporaryBuffer), int(startBit), kd.ctypes.data, vd.ctypes.data,
+                                            fi.ctypes.data, _stream(stream)))
 
     RANKING_AUTO, RANKING_MATCH_MASK, RANKING_COUNTER_RETURN = 0, 1, 2
 
