@@ -146,17 +146,20 @@ THRS_API int thrs_profile_enable(thrs_sorter* s, int on);
 THRS_API int thrs_profile_read(thrs_sorter* s, thrs_profile* out);
 
 /* Multi-GPU layer (no counterpart in the reference, single device: unittest.cpp:22,51).
- * thrs_scatter_pairs: ONE stable 8-bit pass at start_bit whose output is not one array but 256
- * runs: the item with digit d (in sort order, i.e. of getKeyBits ^ order mask) that is the r-th
- * such item of the input goes to ((K*)key_dst[d])[first_index[d] + r], its value likewise through
- * val_dst.  key_dst/val_dst/first_index are HOST arrays of 256 entries holding device addresses
- * (they may point into other GPUs' memory opened with thrs_ipc_open: the pass then IS the
- * exchange over NVLink).  4- and 8-byte values; n < 2^30; temp as for thrs_sort_pairs.
+ * thrs_scatter_pairs: ONE stable pass over the 8-bit digit at start_bit (in sort order, i.e. of
+ * getKeyBits ^ order mask) that splits the input into nbins <= 8 destination bins: bin b takes the
+ * digits [bin_first_digit[b], bin_first_digit[b+1]) (bin_first_digit[0] = 0, ascending, an empty
+ * bin repeats its successor's value).  The r-th input item of bin b goes to
+ * ((K*)key_dst[b])[first_index[b] + r], its value likewise through val_dst: input order is kept
+ * inside a bin.  The four tables are HOST arrays of nbins entries; key_dst / val_dst hold device
+ * addresses and may point into other GPUs' memory opened with thrs_ipc_open — the pass then IS
+ * the exchange over NVLink, in long contiguous bursts.  4- and 8-byte values; n < 2^30; temp as
+ * for thrs_sort_pairs.
  * thrs_ipc_*: cudaIpcGetMemHandle / OpenMemHandle / CloseMemHandle for one-process-per-GPU hosts;
  * the 64-byte handle travels through the host's own channel (torch.distributed here). */
 THRS_API int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uint32_t n, void* temp,
-                                int start_bit, const uint64_t* key_dst, const uint64_t* val_dst,
-                                const uint32_t* first_index, void* stream);
+                                int start_bit, int nbins, const uint32_t* bin_first_digit, const uint64_t* key_dst,
+                                const uint64_t* val_dst, const uint32_t* first_index, void* stream);
 THRS_API int thrs_ipc_export(void* device_ptr, void* handle64);
 THRS_API int thrs_ipc_open(const void* handle64, void** out_device_ptr);
 THRS_API int thrs_ipc_close(void* device_ptr);

@@ -37,14 +37,14 @@ def test_scatter_pairs_emulated_ranks(key, vbytes, ranking):
     rk = [torch.full((max(n, 1),), -1, dtype=kdt, device="cuda") for n in recv_n]
     rv = [torch.full((max(n, 1),), -1, dtype=torch.int32 if vbytes == 4 else torch.int64, device="cuda") for n in recv_n]
     for me in range(world):
-        first = scatter_tables(h, dest, send, me)
-        kd = np.array([rk[int(r)].data_ptr() for r in dest], dtype=np.uint64)
-        vd = np.array([rv[int(r)].data_ptr() for r in dest], dtype=np.uint64)
+        bin_first, first = scatter_tables(dest, send, me)
+        kd = np.array([t_.data_ptr() for t_ in rk], dtype=np.uint64)
+        vd = np.array([t_.data_ptr() for t_ in rv], dtype=np.uint64)
         dk, dv = to_device(slices[me]), to_device(vals[me])
         n = sizes[me]
         tmp = torch.empty(sorter.getTemporaryBufferBytes(n).getTemporaryBufferBytesForSortPairs(), dtype=torch.uint8, device="cuda")
         tmp.fill_(0x5A)
-        sorter.scatterPairs(dk, dv, n, tmp, shift, kd, vd, first)
+        sorter.scatterPairs(dk, dv, n, tmp, shift, bin_first, kd, vd, first)
         assert sorter.lastLaunchCount() == 1
     torch.cuda.synchronize()
     out_k, out_v = [], []
@@ -52,13 +52,12 @@ def test_scatter_pairs_emulated_ranks(key, vbytes, ranking):
         n = recv_n[r]
         got_k = rk[r][:n].cpu().numpy().view(slices[0].dtype)
         got_v = rv[r][:n].cpu().numpy().view(vdt)
-        # expected layout: chunks in source order, each chunk stably partitioned by digit
+        # expected layout: chunks in source order, input order inside a chunk
         ek, ev = [], []
         for me in range(world):
             sel = dest[digit[me]] == r
-            order = np.argsort(digit[me][sel], kind="stable")
-            ek.append(slices[me][sel][order])
-            ev.append(vals[me][sel][order])
+            ek.append(slices[me][sel])
+            ev.append(vals[me][sel])
         assert np.array_equal(got_k, np.concatenate(ek)), f"receive buffer {r}: keys"
         assert np.array_equal(got_v, np.concatenate(ev)), f"receive buffer {r}: values"
         if n:
@@ -74,8 +73,13 @@ def test_scatter_pairs_emulated_ranks(key, vbytes, ranking):
 
 def test_scatter_pairs_rejects_unsupported():
     s = make_sorter("u32", 16)
-    z = np.zeros(256, dtype=np.uint64)
+    z = np.zeros(2, dtype=np.uint64)
     d = torch.zeros(64, dtype=torch.int32, device="cuda")
     tmp = torch.empty(s.getTemporaryBufferBytes(16).getTemporaryBufferBytesForSortPairs(), dtype=torch.uint8, device="cuda")
     with pytest.raises(Exception):
-        s.scatterPairs(d, d, 4, tmp, 24, z, z, np.zeros(256, dtype=np.uint32))
+        s.scatterPairs(d, d, 4, tmp, 24, np.array([0, 128], dtype=np.uint32), z, z, np.zeros(2, dtype=np.uint32))
+    s4 = make_sorter("u32", 4)
+    tmp = torch.empty(s4.getTemporaryBufferBytes(16).getTemporaryBufferBytesForSortPairs(), dtype=torch.uint8, device="cuda")
+    ptrs = np.array([d.data_ptr(), d.data_ptr()], dtype=np.uint64)
+    with pytest.raises(Exception):  # bins must start at digit 0 and ascend
+        s4.scatterPairs(d, d, 4, tmp, 24, np.array([5, 3], dtype=np.uint32), ptrs, ptrs, np.zeros(2, dtype=np.uint32))

@@ -68,8 +68,8 @@ SIGNATURES = {
     "thrs_last_launch_count": (ctypes.c_int, []),
     "thrs_tile_items": (ctypes.c_uint32, [ctypes.c_void_p]),
     "thrs_scatter_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
-                                          ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
-                                          ctypes.c_void_p, ctypes.c_void_p]),
+                                          ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                          ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "thrs_ipc_export": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "thrs_ipc_open": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
     "thrs_ipc_close": (ctypes.c_int, [ctypes.c_void_p]),

@@ -338,12 +338,18 @@ int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, int start
 }
 
 int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uint32_t n, void* temp, int start_bit,
-                       const uint64_t* key_dst, const uint64_t* val_dst, const uint32_t* first_index, void* stream_)
+                       int nbins, const uint32_t* bin_first_digit, const uint64_t* key_dst, const uint64_t* val_dst,
+                       const uint32_t* first_index, void* stream_)
 {
     g_launches = 0;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    if (!s || !temp || !key_dst || !val_dst || !first_index || ((!keys || !values) && n))
+    if (!s || !temp || !bin_first_digit || !key_dst || !val_dst || !first_index || ((!keys || !values) && n))
         return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: NULL argument");
+    if (nbins < 1 || nbins > 8) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: 1..8 bins");
+    if (bin_first_digit[0] != 0) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: bin 0 starts at digit 0");
+    for (int b = 1; b < nbins; ++b)
+        if (bin_first_digit[b] < bin_first_digit[b - 1] || bin_first_digit[b] > 256)
+            return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: bin_first_digit must ascend within [0,256]");
     if (start_bit < 0 || start_bit >= s->kbytes * 8) return fail(THRS_ERR_BIT_RANGE, "thrs_scatter_pairs: start_bit outside the key");
     if (n == 0) return THRS_OK;
     int rc = prepare_device(s);
@@ -358,15 +364,16 @@ int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uin
     if (n > part_items) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_scatter_pairs: n must stay below 2^30");
     Scratch sc{static_cast<uint32_t*>(temp)};
     // control block + the status rows of "pass 0"; the three tables live where pass 1 would
-    CUDA_TRY(cudaMemsetAsync(temp, 0, 4ull * (Scratch::CONTROL_WORDS + Scratch::pass_words(tiles_total)), stream),
+    CUDA_TRY(cudaMemsetAsync(temp, 0, 4ull * (Scratch::CONTROL_WORDS + Scratch::pass_words(tiles_total) + 5 * RADIX), stream),
              "cudaMemsetAsync(scratch)");
     uint32_t* tables = sc.status(1, tiles_total);
     uint32_t* d_first = tables;
     unsigned long long* d_kdst = reinterpret_cast<unsigned long long*>(tables + RADIX);
     unsigned long long* d_vdst = d_kdst + RADIX;
-    CUDA_TRY(cudaMemcpyAsync(d_first, first_index, 4ull * RADIX, cudaMemcpyHostToDevice, stream), "upload first_index");
-    CUDA_TRY(cudaMemcpyAsync(d_kdst, key_dst, 8ull * RADIX, cudaMemcpyHostToDevice, stream), "upload key_dst");
-    CUDA_TRY(cudaMemcpyAsync(d_vdst, val_dst, 8ull * RADIX, cudaMemcpyHostToDevice, stream), "upload val_dst");
+    // the region was zeroed above: bins >= nbins keep offset 0 / pointer 0 and never receive an item
+    CUDA_TRY(cudaMemcpyAsync(d_first, first_index, 4ull * nbins, cudaMemcpyHostToDevice, stream), "upload first_index");
+    CUDA_TRY(cudaMemcpyAsync(d_kdst, key_dst, 8ull * nbins, cudaMemcpyHostToDevice, stream), "upload key_dst");
+    CUDA_TRY(cudaMemcpyAsync(d_vdst, val_dst, 8ull * nbins, cudaMemcpyHostToDevice, stream), "upload val_dst");
     OnesweepArgs a;
     a.keys_in = keys;
     a.keys_out = nullptr;
@@ -383,6 +390,7 @@ int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uin
     a.base_out = nullptr;
     a.peer_keys = d_kdst;
     a.peer_vals = d_vdst;
+    for (int b = 1; b < nbins; ++b) a.thresholds.t[b - 1] = bin_first_digit[b];
     CUDA_TRY(s->table->scatter[s->fast][s->vslot](a, stream), "onesweep_kernel (scatter) launch");
     ++g_launches;
     return THRS_OK;

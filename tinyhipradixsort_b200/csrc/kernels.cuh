@@ -283,6 +283,21 @@ __device__ __forceinline__ void store32(uint32_t* p, uint32_t v) { *p = v; }
 __device__ __forceinline__ void store32(uint2*, uint32_t) {}
 __device__ __forceinline__ void store32(uint4*, uint32_t) {}
 
+// Scatter pass of the multi-GPU layer: the 8-bit digit is mapped to one of <= 8 destination bins
+// through 7 ascending digit thresholds (bin = number of thresholds <= digit; unused ones are 256).
+// Compares only: the ALU pipes are idle in this kernel, the shared-memory pipe is not.
+struct BinThresholds { uint32_t t[7]; };
+template <bool PEER, int KIND, bool DESC, class KeyT>
+__device__ __forceinline__ uint32_t bin_or_digit(KeyT key, uint32_t bit, const BinThresholds& th)
+{
+    const uint32_t d = digit_of<KIND, DESC>(key, bit);
+    if (!PEER) return d;
+    uint32_t b = 0;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) b += (d >= th.t[i]) ? 1u : 0u;
+    return b;
+}
+
 template <int VBYTES> struct ValueOf { using type = uint32_t; };
 template <> struct ValueOf<8> { using type = uint2; };
 template <> struct ValueOf<16> { using type = uint4; };
@@ -333,7 +348,8 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                                               uint32_t bit_c, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
                                               uint32_t* __restrict__ gprefix, const uint32_t* __restrict__ base_in,
                                               uint32_t* __restrict__ base_out, uint32_t tile, bool last_tile,
-                                              size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw)
+                                              size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw,
+                                              const BinThresholds& th)
 {
     using ValT = typename ValueOf<VBYTES>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST, PEER>;
@@ -378,7 +394,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         if (FULL || my0 + j * 32 < tile_valid) {
-            const uint32_t d = digit_of<KIND, DESC>(key[j], bit);
+            const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit, th);
             atomicAdd(tw32 + base_word(d), 1u);
         }
     }
@@ -432,7 +448,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         const bool ok = FULL || my0 + j * 32 < tile_valid;
         // bit_c == bit, passed as a second kernel parameter: ptxas cannot prove it and so does not
         // keep phase A's 16 digit/address temporaries alive (and spill around them) until here
-        const uint32_t d = digit_of<KIND, DESC>(key[j], bit_c);
+        const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit_c, th);
         uint32_t pos;
         if (FAST) {
             // counter-return ranking: the returning atomic hands the lanes that share a counter
@@ -547,7 +563,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         if (FULL || p < tile_valid) {
             if (PACKED) {
                 const uint2 kv = s_kv[p];
-                const uint32_t d = digit_of<KIND, DESC>((KeyT)kv.x, bit);
+                const uint32_t d = bin_or_digit<PEER, KIND, DESC>((KeyT)kv.x, bit, th);
                 const uint32_t dst = s_off[d] + p;
                 KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                 ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
@@ -555,7 +571,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                 store32(vo + dst, kv.y);
             } else {
                 const KeyT kk = s_keys[p];
-                const uint32_t d = digit_of<KIND, DESC>(kk, bit);
+                const uint32_t d = bin_or_digit<PEER, KIND, DESC>(kk, bit, th);
                 const uint32_t dst = s_off[d] + p;
                 KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                 ko[dst] = kk;
@@ -594,9 +610,11 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 // block only ever spins on tickets lower than one it holds, and the block holding the lowest
 // unresolved ticket never spins.  The one partial tile (if any) is done by onesweep_tile<false>.
 // ---------------------------------------------------------------------------------------
-// PEER: the scatter pass of the multi-GPU layer.  Digit d's run goes to peer_keys[d] / peer_vals[d]
-// (device arrays of 256 pointers, possibly into other GPUs' memory over NVLink) at element
-// base_in[d] + rank; keys_out / vals_out are unused.
+// PEER: the scatter pass of the multi-GPU layer.  Items are binned by destination (bin_or_digit), bin
+// b's items go, in input order, to peer_keys[b] / peer_vals[b] (device arrays of pointers, possibly
+// into other GPUs' memory over NVLink) from element base_in[b] on; keys_out / vals_out are unused.
+// A tile's run for one destination is ~TILE/ranks contiguous items, so the peer stores are long
+// full-line bursts (a 256-way digit split would send ~160-byte runs over the link).
 template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST, bool PEER>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
@@ -605,7 +623,8 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 uint32_t n, uint32_t bit, uint32_t bit_c, uint32_t* __restrict__ status, uint32_t* __restrict__ gsum,
                 uint32_t* __restrict__ gprefix, uint32_t* __restrict__ ticket,
                 const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out,
-                const unsigned long long* __restrict__ peer_keys, const unsigned long long* __restrict__ peer_vals)
+                const unsigned long long* __restrict__ peer_keys, const unsigned long long* __restrict__ peer_vals,
+                const BinThresholds th)
 {
     using ValT = typename ValueOf<VBYTES>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST, PEER>;
@@ -670,7 +689,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
             if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
             // ---- phase A(tile): per-warp digit counts
 #pragma unroll
-            for (int j = 0; j < ITEMS; ++j) atomicAdd(tw32 + base_word(digit_of<KIND, DESC>(key[j], bit)), 1u);
+            for (int j = 0; j < ITEMS; ++j) atomicAdd(tw32 + base_word(bin_or_digit<PEER, KIND, DESC>(key[j], bit, th)), 1u);
             if (PAIRS) {
                 const ValT* vin = vals_in + tile_base + my0;
 #pragma unroll
@@ -751,7 +770,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const uint32_t p = k * THREADS + tid;
                 if (PACKED) {
                     const uint2 kv = s_kv[p];
-                    const uint32_t d = digit_of<KIND, DESC>((KeyT)kv.x, bit);
+                    const uint32_t d = bin_or_digit<PEER, KIND, DESC>((KeyT)kv.x, bit, th);
                     const uint32_t dst = s_off[d] + p;
                     KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                     ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
@@ -759,7 +778,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                     store32(vo + dst, kv.y);
                 } else {
                     const KeyT kk = s_keys[p];
-                    const uint32_t d = digit_of<KIND, DESC>(kk, bit);
+                    const uint32_t d = bin_or_digit<PEER, KIND, DESC>(kk, bit, th);
                     const uint32_t dst = s_off[d] + p;
                     KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                     ko[dst] = kk;
@@ -780,7 +799,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
             // bit_c == bit (second kernel parameter): keeps ptxas from holding phase A's temporaries
-            const uint32_t d = digit_of<KIND, DESC>(key[j], bit_c);
+            const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit_c, th);
             uint32_t pos;
             if (FAST) {
                 pos = atomicAdd(tw32 + d, 1u); // old value = stable position (probe.cuh)
@@ -842,7 +861,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         const size_t tile_base = (size_t)tile * TILE;
         onesweep_tile<false, FAST, PEER, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
             key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
-            base_out, tile, true, tile_base, (uint32_t)(n - tile_base), smem_raw);
+            base_out, tile, true, tile_base, (uint32_t)(n - tile_base), smem_raw, th);
     }
 }
 

@@ -60,6 +60,7 @@ struct OnesweepArgs {
     // scatter pass only: device arrays of 256 destination pointers (keys / values per digit)
     const unsigned long long* peer_keys = nullptr;
     const unsigned long long* peer_vals = nullptr;
+    BinThresholds thresholds = {{256u, 256u, 256u, 256u, 256u, 256u, 256u}};
 };
 
 struct KernelTable {
@@ -142,7 +143,7 @@ cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
     onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER><<<grid, T::THREADS, SM::BYTES, stream>>>(
         static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
         static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out,
-        a.peer_keys, a.peer_vals);
+        a.peer_keys, a.peer_vals, a.thresholds);
     return cudaGetLastError();
 }
 

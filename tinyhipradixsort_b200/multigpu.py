@@ -9,8 +9,8 @@ SURVEY.md 8(e):
   2. all_gather of the 256-bin histograms (2 KiB per rank) -> identical table on every rank;
   3. splitters on digit boundaries: bucket b goes to rank floor(P * items_before(b) / N), so
      equal keys never straddle ranks and the destination is monotone in the digit;
-  4. one stable onesweep pass on the top digit (thrs_sort_pairs on bits [top-8, top)) groups the
-     slice by destination without reordering anything inside a bucket;
+  4. one stable onesweep pass on the top digit groups the slice by destination without
+     reordering anything inside a destination;
   5. exchange; chunks land in SOURCE-RANK order.  On GPUs steps 4+5 are ONE kernel: the pass of
      step 4 stores every digit run straight into its destination rank's receive buffer over
      NVLink (thrs_scatter_pairs with CUDA-IPC peer pointers, `scatter_exchange`), followed by a
@@ -49,18 +49,15 @@ def plan_partition(all_hists, world):
     return dest, send
 
 
-def scatter_tables(all_hists, dest, send, me):
-    """Where rank `me`'s run of digit d starts inside its destination's receive buffer (elements):
-    chunks are laid out in source-rank order, digits ascending inside a chunk."""
-    h = np.asarray(all_hists, dtype=np.int64).reshape(-1, 256)
-    first = np.zeros(256, dtype=np.int64)
+def scatter_tables(dest, send, me):
+    """Tables of the fused exchange for source rank `me`: (bin_first_digit[world], first[world]).
+    Bin r = the digits whose destination is rank r (dest is monotone in the digit); rank me's
+    items for rank r land in r's receive buffer from element sum(send[:me, r]) on, in input order,
+    so chunks lie in source-rank order."""
     world = send.shape[0]
-    for r in range(world):
-        start = int(send[:me, r].sum())
-        for d in np.nonzero(dest == r)[0]:
-            first[d] = start
-            start += int(h[me, d])
-    return first
+    bin_first = np.array([int(np.searchsorted(dest, r, side="left")) for r in range(world)], dtype=np.int64)
+    first = np.array([int(send[:me, r].sum()) for r in range(world)], dtype=np.int64)
+    return bin_first, first
 
 
 class CudaLocalOps:
@@ -143,12 +140,12 @@ class CudaLocalOps:
         v = torch.as_tensor(_Raw(self._xbuf.data() + self._xvoff, max(count, 1), ts[val_dtype]), device="cuda")
         return k[:count], v[:count]
 
-    def scatter_exchange(self, keys, vals, n, start_bit, dest, first):
-        """Steps 4+5 fused: digit d's run -> receive buffer of rank dest[d] at element first[d]."""
-        kd = np.array([self._xbases[int(r)] + self._xkoff for r in dest], dtype=np.uint64)
-        vd = np.array([self._xbases[int(r)] + self._xvoff for r in dest], dtype=np.uint64)
+    def scatter_exchange(self, keys, vals, n, start_bit, bin_first, first):
+        """Steps 4+5 fused: this rank's items for rank r -> r's receive buffer from element first[r] on."""
+        kd = np.array([b + self._xkoff for b in self._xbases], dtype=np.uint64)
+        vd = np.array([b + self._xvoff for b in self._xbases], dtype=np.uint64)
         if n:
-            self.sorter.scatterPairs(keys, vals, n, self._temp(n), start_bit, kd, vd, first.astype(np.uint32))
+            self.sorter.scatterPairs(keys, vals, n, self._temp(n), start_bit, bin_first, kd, vd, first)
 
 
 class DistributedRadixSort:
@@ -235,9 +232,11 @@ class DistributedRadixSort:
             dist.all_gather_object(handles, handle, group=self.group)
             ops.exchange_open(handles, self.rank)
             self._xcap = cap
-        first = scatter_tables(all_h, dest, send, self.rank)
+        if P > 8:
+            raise ValueError("the fused exchange splits into at most 8 destinations (one NVSwitch box)")
+        bin_first, first = scatter_tables(dest, send, self.rank)
         # 4+5: the partition pass stores straight into the destination ranks' receive buffers
-        ops.scatter_exchange(keys, vals, n, bits - 8, dest, first)
+        ops.scatter_exchange(keys, vals, n, bits - 8, bin_first, first)
         # "everyone has written": a one-word all_reduce ordered after the scatter kernel on every rank
         flag = torch.ones(1, dtype=torch.int32, device=keys.device)
         dist.all_reduce(flag, group=self.group)

@@ -254,20 +254,22 @@ class RadixSort:
                 "pass_ms": [p.pass_ms[i] for i in range(p.passes)], "copyback_ms": p.copyback_ms,
                 "total_ms": p.total_ms, "passes": p.passes, "parts": p.parts}
 
-    def scatterPairs(self, inputKeyBuffer, inputValueBuffer, numberOfInputs, temporaryBuffer, startBit, keyDst, valDst,
-                     firstIndex, stream=None):
-        """One stable 8-bit pass whose 256 runs go to per-digit destinations (thrs_scatter_pairs):
-        keyDst / valDst are 256 device addresses (own or peer memory), firstIndex 256 element offsets."""
+    def scatterPairs(self, inputKeyBuffer, inputValueBuffer, numberOfInputs, temporaryBuffer, startBit, binFirstDigit,
+                     keyDst, valDst, firstIndex, stream=None):
+        """One stable pass that splits the input into len(binFirstDigit) <= 8 destination bins by the
+        8-bit digit at startBit (thrs_scatter_pairs): bin b's items go, in input order, to device
+        address keyDst[b] / valDst[b] (own or peer memory) from element firstIndex[b] on."""
         import numpy as np
 
+        bf = np.ascontiguousarray(binFirstDigit, dtype=np.uint32)
         kd = np.ascontiguousarray(keyDst, dtype=np.uint64)
         vd = np.ascontiguousarray(valDst, dtype=np.uint64)
         fi = np.ascontiguousarray(firstIndex, dtype=np.uint32)
-        if kd.shape != (256,) or vd.shape != (256,) or fi.shape != (256,):
-            raise ThrsError(1, "scatterPairs: the three tables have 256 entries")
+        if not (bf.ndim == 1 and bf.shape == kd.shape == vd.shape == fi.shape):
+            raise ThrsError(1, "scatterPairs: the four tables have one entry per bin")
         _check(self._lib.thrs_scatter_pairs(self._h, _ptr(inputKeyBuffer), _ptr(inputValueBuffer), int(numberOfInputs),
-                                            _ptr(temporaryBuffer), int(startBit), kd.ctypes.data, vd.ctypes.data,
-                                            fi.ctypes.data, _stream(stream)))
+                                            _ptr(temporaryBuffer), int(startBit), int(bf.shape[0]), bf.ctypes.data,
+                                            kd.ctypes.data, vd.ctypes.data, fi.ctypes.data, _stream(stream)))
 
     RANKING_AUTO, RANKING_MATCH_MASK, RANKING_COUNTER_RETURN = 0, 1, 2
 
