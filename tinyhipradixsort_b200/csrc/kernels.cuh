@@ -287,6 +287,14 @@ __device__ __forceinline__ void store32(uint4*, uint32_t) {}
 // through 7 ascending digit thresholds (bin = number of thresholds <= digit; unused ones are 256).
 // Compares only: the ALU pipes are idle in this kernel, the shared-memory pipe is not.
 struct BinThresholds { uint32_t t[7]; };
+template <int KIND, bool DESC> __device__ __forceinline__ uint32_t shifted_key_bits(uint32_t raw, uint32_t bit)
+{
+    return key_bits32<KIND, DESC>(raw) >> bit;
+}
+template <int KIND, bool DESC> __device__ __forceinline__ uint32_t shifted_key_bits(uint64_t raw, uint32_t bit)
+{
+    return (uint32_t)(key_bits64<KIND, DESC>(raw) >> bit);
+}
 template <bool PEER, int KIND, bool DESC, class KeyT>
 __device__ __forceinline__ uint32_t bin_or_digit(KeyT key, uint32_t bit, const BinThresholds& th)
 {
@@ -683,13 +691,29 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (!cur && !have_prev) break;
         const size_t tile_base = (size_t)tile * TILE;
         uint32_t count = 0;
+        bool warp_one_digit = false;
+        uint32_t warp_digit = 0;
         ValT val[PAIRS ? ITEMS : 1];
         if (cur) {
             // ticket of the tile after this one (slot alternates: it is read a full iteration later)
             if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
-            // ---- phase A(tile): per-warp digit counts
+            // ---- phase A(tile): per-warp digit counts; and does this warp hold ONE digit only?
+            // (all-equal keys, zero high bytes, sorted input: the ranking atomics would serialise
+            // 32-way on one counter, while the positions are simply consecutive)
+            // (sameness is accumulated on the shifted key bits: one LOP3 per item)
+            const uint32_t x_first = __shfl_sync(0xffffffffu, shifted_key_bits<KIND, DESC>(key[0], bit), 0);
+            const uint32_t d_first = PEER ? bin_or_digit<PEER, KIND, DESC>(key[0], bit, th) : (x_first & 0xFFu);
+            uint32_t diff = 0;
 #pragma unroll
-            for (int j = 0; j < ITEMS; ++j) atomicAdd(tw32 + base_word(bin_or_digit<PEER, KIND, DESC>(key[j], bit, th)), 1u);
+            for (int j = 0; j < ITEMS; ++j) {
+                const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit, th);
+                diff |= shifted_key_bits<KIND, DESC>(key[j], bit) ^ x_first;
+                atomicAdd(tw32 + base_word(d), 1u);
+            }
+            // PEER bins several digits together: equal digits are sufficient there, not necessary
+            const bool same = (diff & 0xFFu) == 0u;
+            warp_one_digit = __all_sync(0xffffffffu, same);
+            warp_digit = d_first;
             if (PAIRS) {
                 const ValT* vin = vals_in + tile_base + my0;
 #pragma unroll
@@ -796,33 +820,47 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         const uint32_t next_tile = s_misc[12 + (iter & 1u)];
         const uint32_t lane_bit = 1u << lane;
         const uint32_t lane_lt = lane_bit - 1u;
+        if (warp_one_digit) {
+            // one digit in the whole warp: its items keep their order at consecutive positions
+            const uint32_t first_pos = tw32[base_word(warp_digit)] + lane;
 #pragma unroll
-        for (int j = 0; j < ITEMS; ++j) {
-            // bit_c == bit (second kernel parameter): keeps ptxas from holding phase A's temporaries
-            const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit_c, th);
-            uint32_t pos;
-            if (FAST) {
-                pos = atomicAdd(tw32 + d, 1u); // old value = stable position (probe.cuh)
-                __syncwarp();
-            } else {
-                const bool swapped = (d >> 4) & 1u;
-                atomicOr(tw32 + mask_word(d), lane_bit);
-                __syncwarp();
-                const uint2 raw = tw[d];
-                const uint2 e = swapped ? make_uint2(raw.y, raw.x) : raw;
-                const uint32_t lower = __popc(e.x & lane_lt);
-                __syncwarp();
-                if (lower == 0) {
-                    const uint32_t nb = e.y + __popc(e.x);
-                    tw[d] = swapped ? make_uint2(nb, 0u) : make_uint2(0u, nb);
+            for (int j = 0; j < ITEMS; ++j) {
+                const uint32_t pos = first_pos + j * 32;
+                if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
+                else {
+                    s_keys[pos] = key[j];
+                    if (PAIRS) s_vals[pos] = val[j];
                 }
-                __syncwarp();
-                pos = e.y + lower;
             }
-            if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
-            else {
-                s_keys[pos] = key[j];
-                if (PAIRS) s_vals[pos] = val[j];
+        } else {
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j) {
+                // bit_c == bit (second kernel parameter): keeps ptxas from holding phase A's temporaries
+                const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit_c, th);
+                uint32_t pos;
+                if (FAST) {
+                    pos = atomicAdd(tw32 + d, 1u); // old value = stable position (probe.cuh)
+                    __syncwarp();
+                } else {
+                    const bool swapped = (d >> 4) & 1u;
+                    atomicOr(tw32 + mask_word(d), lane_bit);
+                    __syncwarp();
+                    const uint2 raw = tw[d];
+                    const uint2 e = swapped ? make_uint2(raw.y, raw.x) : raw;
+                    const uint32_t lower = __popc(e.x & lane_lt);
+                    __syncwarp();
+                    if (lower == 0) {
+                        const uint32_t nb = e.y + __popc(e.x);
+                        tw[d] = swapped ? make_uint2(nb, 0u) : make_uint2(0u, nb);
+                    }
+                    __syncwarp();
+                    pos = e.y + lower;
+                }
+                if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
+                else {
+                    s_keys[pos] = key[j];
+                    if (PAIRS) s_vals[pos] = val[j];
+                }
             }
         }
         // this warp's table row is private until the next scan: zero it for the next phase A
