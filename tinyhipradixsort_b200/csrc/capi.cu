@@ -61,6 +61,7 @@ struct thrs_sorter {
     // ranking of the onesweep kernels: requested (THRS_RANKING_*) and resolved (0 match-mask, 1 counter-return)
     int ranking_request = THRS_RANKING_AUTO;
     int fast = 0;
+    int force_multiblock = 0; // tests: run small inputs through the histogram + onesweep path too
     int probe_in_order = 0;
     unsigned long long probe_groups = 0;
     // workspace of thrs_sort_host (grown on demand, guarded)
@@ -163,6 +164,7 @@ static int prepare_device(thrs_sorter* s)
                 e = s->table->prepare[f][v]();
                 if (e == cudaSuccess && s->table->prepare_scatter[f][v]) e = s->table->prepare_scatter[f][v]();
             }
+        for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare_small[v]();
         if (e == cudaSuccess) e = s->table->prepare_histogram();
         // which ranking this device can run exactly (probe.cuh); once per process and device
         if (e == cudaSuccess) {
@@ -218,19 +220,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     s->fast = (s->ranking_request == THRS_RANKING_MATCH_MASK) ? 0
               : (s->ranking_request == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
 
-    thrs_temp_def def;
-    thrs_temp_bytes(s, n, &def);
-    Scratch sc{static_cast<uint32_t*>(temp)};
-    char* key_out = static_cast<char*>(temp) + def.pSumBuffer;
-    char* val_out = key_out + def.keyOutBuffer;
-
     const int vslot = pairs ? s->vslot : 0;
-    const uint32_t tile = s->table->tile_items[s->fast][vslot];
-    const uint64_t tiles_total = div_up(n, tile);
-    const uint64_t part_items = (uint64_t)(VALUE_MASK / tile) * tile; // < 2^30, whole tiles
-    const int parts = (int)div_up(n, part_items);
-    if (parts > MAX_PARTS) return fail(THRS_ERR_INVALID_ARGUMENT, "sort: too many parts");
-
     int ev_i = 0;
     auto mark = [&]() -> cudaError_t {
         if (!s->profiling) return cudaSuccess;
@@ -240,6 +230,32 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
         }
         return cudaEventRecord(s->ev[ev_i++], stream);
     };
+
+    // small inputs: the whole sort in one block, in place, one launch, no scratch (small_sort.cuh)
+    if (n <= SMALL_SORT_MAX && !s->force_multiblock) {
+        for (int i = 0; i < 3; ++i) CUDA_TRY(mark(), "profile event");
+        CUDA_TRY(s->table->small[vslot](keys, values, n, (uint32_t)start_bits, passes, stream), "small_sort_kernel launch");
+        ++g_launches;
+        CUDA_TRY(mark(), "profile event");
+        s->ev_count = ev_i;
+        s->ev_passes = 1;
+        s->ev_parts = 1;
+        s->ev_copyback = false;
+        return THRS_OK;
+    }
+
+    thrs_temp_def def;
+    thrs_temp_bytes(s, n, &def);
+    Scratch sc{static_cast<uint32_t*>(temp)};
+    char* key_out = static_cast<char*>(temp) + def.pSumBuffer;
+    char* val_out = key_out + def.keyOutBuffer;
+
+    const uint32_t tile = s->table->tile_items[s->fast][vslot];
+    const uint64_t tiles_total = div_up(n, tile);
+    const uint64_t part_items = (uint64_t)(VALUE_MASK / tile) * tile; // < 2^30, whole tiles
+    const int parts = (int)div_up(n, part_items);
+    if (parts > MAX_PARTS) return fail(THRS_ERR_INVALID_ARGUMENT, "sort: too many parts");
+
     CUDA_TRY(mark(), "profile event");
 
     // zero: histograms, bases, tickets, counters and the status rows of the passes we run
@@ -513,6 +529,13 @@ int thrs_set_ranking(thrs_sorter* s, int ranking)
         return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_ranking: bad ranking");
     s->ranking_request = ranking;
     s->fast = (ranking == THRS_RANKING_MATCH_MASK) ? 0 : (ranking == THRS_RANKING_COUNTER_RETURN) ? 1 : s->probe_in_order;
+    return THRS_OK;
+}
+
+int thrs_set_small_path(thrs_sorter* s, int enabled)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_small_path: NULL sorter");
+    s->force_multiblock = enabled ? 0 : 1;
     return THRS_OK;
 }
 

@@ -4,6 +4,7 @@
 // -DDESCENDING_ORDER (tinyhipradixsort.hpp:754-791).
 #pragma once
 #include "kernels.cuh"
+#include "small_sort.cuh"
 
 namespace thrs_b200 {
 
@@ -75,6 +76,9 @@ struct KernelTable {
     // scatter pass (per-digit destination pointers); 4- and 8-byte values only, else nullptr
     cudaError_t (*scatter[2][4])(const OnesweepArgs& a, cudaStream_t stream);
     cudaError_t (*prepare_scatter[2][4])();
+    // one-block sort for n <= SMALL_SORT_MAX (small_sort.cuh)
+    cudaError_t (*small[4])(void* keys, void* vals, uint32_t n, uint32_t start_bit, int passes, cudaStream_t stream);
+    cudaError_t (*prepare_small[4])();
 };
 
 template <class KeyT, int KIND, bool DESC, int PASSES>
@@ -178,7 +182,11 @@ const KernelTable* make_table()
         {{nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, false, true>, &launch_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},
          {nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, true, true>, &launch_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}},
         {{nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},
-         {nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, true, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}}};
+         {nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, true, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}},
+        {&launch_small_sort<KeyT, KIND, DESC, 0>, &launch_small_sort<KeyT, KIND, DESC, 4>,
+         &launch_small_sort<KeyT, KIND, DESC, 8>, &launch_small_sort<KeyT, KIND, DESC, 16>},
+        {&prepare_small_sort<KeyT, KIND, DESC, 0>, &prepare_small_sort<KeyT, KIND, DESC, 4>,
+         &prepare_small_sort<KeyT, KIND, DESC, 8>, &prepare_small_sort<KeyT, KIND, DESC, 16>}};
     return &t;
 }
 

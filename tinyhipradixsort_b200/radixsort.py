@@ -271,6 +271,12 @@ class RadixSort:
                                             _ptr(temporaryBuffer), int(startBit), int(bf.shape[0]), bf.ctypes.data,
                                             kd.ctypes.data, vd.ctypes.data, fi.ctypes.data, _stream(stream)))
 
+    SMALL_SORT_MAX = 4096
+
+    def setSmallPath(self, enabled):
+        """Enable/disable the one-block path for n <= SMALL_SORT_MAX (thrs_set_small_path)."""
+        _check(self._lib.thrs_set_small_path(self._h, int(bool(enabled))))
+
     RANKING_AUTO, RANKING_MATCH_MASK, RANKING_COUNTER_RETURN = 0, 1, 2
 
     def setRanking(self, ranking):
