@@ -325,7 +325,8 @@ struct OnesweepSmem {
     static constexpr size_t OFF_KEY = OFF_VAL + VAL_BYTES;
     static constexpr size_t OFF_BIN = OFF_KEY + KEY_BYTES;
     static constexpr size_t OFF_PTR = OFF_BIN + RADIX * 4 + 64; // 8-byte aligned
-    static constexpr size_t BYTES = OFF_PTR + (PEER ? 2 * RADIX * 8 : 0);
+    static constexpr size_t OFF_RUN = OFF_PTR + 2 * RADIX * 8; // PEER: tile-local start and length of 8 bins
+    static constexpr size_t BYTES = PEER ? OFF_RUN + 64 : OFF_PTR;
 };
 
 // Keys of one tile into registers, warp-striped.  `valid` == TILE takes the unguarded path.
@@ -652,6 +653,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     uint32_t* s_misc = s_off + RADIX;
     unsigned long long* s_kptr = reinterpret_cast<unsigned long long*>(smem_raw + SM::OFF_PTR);
     unsigned long long* s_vptr = s_kptr + RADIX;
+    uint32_t* s_run = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_RUN); // PEER only
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -784,11 +786,41 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
             const uint32_t gbase = base_in[tid] + excl;
             s_off[tid] = gbase - p_bin_start;
             if (base_out != nullptr && p_tile == num_tiles - 1) base_out[tid] = gbase + p_count;
+            if (PEER && tid < 8) {
+                s_run[tid] = p_bin_start;
+                s_run[8 + tid] = p_count;
+            }
         }
         __syncthreads();
 
-        // ---- read-out(prev): consecutive threads take consecutive tile-sorted slots
-        if (have_prev) {
+        // ---- read-out(prev)
+        if (PEER && have_prev) {
+            // <= 8 long runs, one per destination.  Lanes are mapped to DESTINATION elements so that
+            // every warp store is one whole aligned 128-byte line: a store that straddles two lines
+            // travels over NVLink as two short packets.
+            for (int b = 0; b < 8; ++b) {
+                const uint32_t len = s_run[8 + b];
+                if (len == 0u) continue;
+                const uint32_t bs = s_run[b];
+                const uint32_t gfirst = s_off[b] + bs; // element index of the run's first item at its destination
+                const uint32_t a = gfirst & 31u;
+                KeyT* ko = reinterpret_cast<KeyT*>(s_kptr[b]) + gfirst;
+                ValT* vo = reinterpret_cast<ValT*>(s_vptr[b]) + gfirst;
+                for (uint32_t idx = tid; idx < len + a; idx += THREADS) {
+                    if (idx >= a) {
+                        const uint32_t e = idx - a;
+                        if (PACKED) {
+                            const uint2 kv = s_kv[bs + e];
+                            ko[e] = (KeyT)kv.x;
+                            store32(vo + e, kv.y);
+                        } else {
+                            ko[e] = s_keys[bs + e];
+                            if (PAIRS) vo[e] = s_vals[bs + e];
+                        }
+                    }
+                }
+            }
+        } else if (have_prev) { // consecutive threads take consecutive tile-sorted slots
 #pragma unroll
             for (int k = 0; k < ITEMS; ++k) {
                 const uint32_t p = k * THREADS + tid;
