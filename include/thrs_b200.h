@@ -164,6 +164,23 @@ THRS_API int thrs_ipc_export(void* device_ptr, void* handle64);
 THRS_API int thrs_ipc_open(const void* handle64, void** out_device_ptr);
 THRS_API int thrs_ipc_close(void* device_ptr);
 
+/* Single-process multi-GPU sort (SURVEY.md 8(b) plan: thrs_mg_create / thrs_mg_sort_pairs /
+ * thrs_mg_destroy): one host thread drives up to 8 peer-capable devices of one box.  keys[g] /
+ * values[g] are device pointers on device_ids[g] holding counts[g] items (< 2^30 each, 64-bit
+ * counts at this layer; the inputs are only read).  out_keys[g] / out_values[g] are buffers on the
+ * same devices with room for out_capacity[g] items.  On return out_counts[g] items lie in each
+ * output, and the concatenation over g = 0..ndev-1 is exactly std::stable_sort of the concatenated
+ * inputs (ties in (device, position) order).  The split is by whole top-digit buckets, so an
+ * output can receive more than total/ndev items: if a capacity is too small the call fails with
+ * THRS_ERR_INVALID_ARGUMENT and the needed sizes in out_counts.  Blocking; 4- and 8-byte values. */
+typedef struct thrs_mg thrs_mg;
+THRS_API int thrs_mg_create(int ndev, const int* device_ids, const thrs_config* cfg, thrs_mg** out);
+THRS_API void thrs_mg_destroy(thrs_mg* m);
+THRS_API int thrs_mg_sort_pairs(thrs_mg* m, const void* const* keys, const void* const* values, const uint64_t* counts,
+                                void* const* out_keys, void* const* out_values, const uint64_t* out_capacity,
+                                uint64_t* out_counts);
+THRS_API const char* thrs_mg_last_error(void);
+
 /* Ranking used by the onesweep kernels (no counterpart in the reference, which has one scheme,
  * kernel.cu:293-345).  COUNTER_RETURN takes the old value of a returning shared-memory atomicAdd
  * as the stable rank; it is exact only where lanes that hit one counter in one warp instruction

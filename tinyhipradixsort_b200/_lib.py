@@ -73,6 +73,14 @@ SIGNATURES = {
     "thrs_ipc_export": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "thrs_ipc_open": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
     "thrs_ipc_close": (ctypes.c_int, [ctypes.c_void_p]),
+    "thrs_mg_create": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(thrs_config),
+                                      ctypes.POINTER(ctypes.c_void_p)]),
+    "thrs_mg_destroy": (None, [ctypes.c_void_p]),
+    "thrs_mg_sort_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
+                                          ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_void_p),
+                                          ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint64),
+                                          ctypes.POINTER(ctypes.c_uint64)]),
+    "thrs_mg_last_error": (ctypes.c_char_p, []),
     "thrs_set_small_path": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_set_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_get_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),

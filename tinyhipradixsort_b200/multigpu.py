@@ -412,3 +412,59 @@ def bench(args, dist, rank, world, dev, g):
     dist.barrier()
     dist.destroy_process_group()
     return 0 if verified else 1
+
+
+class SingleProcessMultiGpuSort:
+    """thrs_mg_*: the same partitioned sort driven from ONE process over peer-capable devices
+    (device ids may repeat, which emulates several ranks on one GPU for tests)."""
+
+    def __init__(self, device_ids, key="u32", value_bytes=4, descending=False):
+        import ctypes
+
+        from . import _lib
+        from .radixsort import KeyType, SortOrder, _check
+
+        self._ct = ctypes
+        self._lib = _lib.load()
+        cfg = _lib.thrs_config()
+        self._lib.thrs_config_default(ctypes.byref(cfg))
+        cfg.key_type = {"u32": 0, "u64": 1, "f32": 2, "f64": 3}[key] if not isinstance(key, KeyType) else int(key)
+        cfg.value_type = {4: 0, 8: 1, 16: 2}[value_bytes]
+        cfg.sort_order = 1 if descending else 0
+        self.ids = list(device_ids)
+        arr = (ctypes.c_int * len(self.ids))(*self.ids)
+        self._h = ctypes.c_void_p()
+        rc = self._lib.thrs_mg_create(len(self.ids), arr, ctypes.byref(cfg), ctypes.byref(self._h))
+        if rc:
+            raise RuntimeError(f"thrs_mg_create rc={rc}: {self._lib.thrs_mg_last_error().decode()}")
+
+    def sort_pairs(self, keys, values, out_keys, out_values):
+        """keys/values: lists of CUDA tensors (one per device slot); out_*: lists of output tensors.
+        Returns the list of item counts that landed in each output."""
+        ct = self._ct
+        n = len(self.ids)
+        vp = ct.c_void_p * n
+        u64 = ct.c_uint64 * n
+        k = vp(*[t.data_ptr() for t in keys])
+        v = vp(*[t.data_ptr() for t in values])
+        ok = vp(*[t.data_ptr() for t in out_keys])
+        ov = vp(*[t.data_ptr() for t in out_values])
+        counts = u64(*[int(t.shape[0]) for t in keys])
+        cap = u64(*[int(t.shape[0]) for t in out_keys])
+        out = u64()
+        rc = self._lib.thrs_mg_sort_pairs(self._h, k, v, counts, ok, ov, cap, out)
+        self.last_needed = [int(x) for x in out]
+        if rc:
+            raise RuntimeError(f"thrs_mg_sort_pairs rc={rc}: {self._lib.thrs_mg_last_error().decode()}")
+        return [int(x) for x in out]
+
+    def close(self):
+        if self._h:
+            self._lib.thrs_mg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
