@@ -178,7 +178,12 @@ def run_reference(args):
     ge.build(quiet=True, only_missing=True)
     import oracle
 
-    threads = oracle.max_threads()
+    # torchrun exports OMP_NUM_THREADS=1: count the cores this process may run on instead
+    try:
+        threads = len(os.sched_getaffinity(0))
+    except AttributeError:
+        threads = os.cpu_count() or 1
+    threads = max(threads, oracle.max_threads())
     log2n = args.cpu_log2n
     keys0, vals0 = cpu_sample(log2n)
     n = keys0.shape[0]
