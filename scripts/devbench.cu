@@ -97,12 +97,19 @@ int main(int argc, char** argv)
     if (void* f = dlsym(RTLD_DEFAULT, "thrs_dev_phase")) { // dev-only variant built with -DTHRS_PHASE_TIMING
         unsigned long long ph[16];
         ((void (*)(unsigned long long*, int))f)(ph, 1);
+        // pipelined kernel: slots 7..15 (the straight-line tail tile uses 0..7, negligible)
+        const int slot[9] = {8, 9, 10, 11, 12, 13, 14, 15, 7};
+        const char* names[9] = {"issue-prefetch", "phaseA", "bar1", "scan", "resolve", "bar2", "readout", "bar3", "phaseC"};
         unsigned long long tot = 0;
-        for (int i = 0; i < 8; ++i) tot += ph[i];
-        const char* names[8] = {"load", "phaseA", "bar1", "scan+bar2", "phaseC", "lookback", "bar3", "readout"};
-        printf("phase share of warp-0 cycles:");
-        for (int i = 0; i < 8; ++i) printf(" %s %.1f%%", names[i], 100.0 * ph[i] / tot);
-        printf("\n");
+        for (int i = 0; i < 9; ++i) tot += ph[slot[i]];
+        printf("phase share of thread-0 cycles:");
+        for (int i = 0; i < 9; ++i) printf(" %s %.1f%%", names[i], 100.0 * ph[slot[i]] / tot);
+        printf("\nlook-back (thread 0): resolves %llu, status re-polls %llu, prefix inside group %llu, group poll rounds %llu\n", ph[0], ph[1], ph[3], ph[4]);
+    }
+    if (void* f = dlsym(RTLD_DEFAULT, "thrs_dev_trace")) {
+        static unsigned long long tr[6 * 32768];
+        ((void (*)(unsigned long long*))f)(tr);
+        if (FILE* fp = fopen("gpurun_out/trace.bin", "wb")) { fwrite(tr, 8, 6 * 32768, fp); fclose(fp); }
     }
     int passes = (eb - sb) / 8;
     double bytes = (double)n * 4 + (double)passes * 2 * n * (pairs ? 8 : 4);

@@ -17,4 +17,9 @@ extern "C" __attribute__((visibility("default"))) void thrs_dev_phase(unsigned l
         cudaMemcpyToSymbol(thrs_b200::g_phase, z, sizeof(z));
     }
 }
+extern "C" __attribute__((visibility("default"))) void thrs_dev_trace(unsigned long long* out)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, thrs_b200::g_trace, sizeof(unsigned long long) * 6 * 32768);
+}
 #endif

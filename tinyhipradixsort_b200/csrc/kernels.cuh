@@ -88,7 +88,18 @@ static __device__ unsigned long long g_phase[16];
         }                                                                    \
     } while (0)
 #define PHASE_BEGIN() long long phase_t0 = clock64()
+#define LB_COUNT(i) do { if (threadIdx.x == 0) atomicAdd(&g_phase[i], 1ull); } while (0)
+static __device__ unsigned long long g_trace[6][32768];
+__device__ __forceinline__ unsigned long long trace_now()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TRACE(ev, tile_) do { if (threadIdx.x == 0 && (tile_) < 32768u) g_trace[ev][tile_] = trace_now(); } while (0)
 #else
+#define TRACE(ev, tile_) do { } while (0)
+#define LB_COUNT(i) do { } while (0)
 #define PHASE_MARK(i) do { } while (0)
 #define PHASE_BEGIN() do { } while (0)
 #endif
@@ -390,16 +401,11 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
     constexpr int ROW = FAST ? RADIX : 2 * RADIX; // 32-bit words per warp row
     if (FAST) tw32 = tbl32 + warp * RADIX;
 
-    PHASE_BEGIN();
     const uint32_t my0 = warp * (32 * ITEMS) + lane;
     // ticket of the tile after this one: requested now, read after the scan's barriers
     if (tid == 0) s_misc[14] = atomicAdd(ticket, 1u);
 
     // ---- phase A: per-warp digit counts
-#ifdef THRS_PHASE_TIMING
-    if (key[ITEMS - 1] == 0x12345677u && key[0] == 0x7654321u) g_phase[15] = 1; // wait for the loads
-    PHASE_MARK(0);
-#endif
 #pragma unroll
     for (int j = 0; j < ITEMS; ++j) {
         if (FULL || my0 + j * 32 < tile_valid) {
@@ -418,9 +424,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
             else val[j] = ValT();
         }
     }
-    PHASE_MARK(1);
     __syncthreads();
-    PHASE_MARK(2);
 
     // ---- scan: thread d owns digit d
     uint32_t count = 0, bin_start;
@@ -447,7 +451,6 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         }
     }
     __syncthreads();
-    PHASE_MARK(3);
 
     // ---- phase C: rank inside the warp step and stage at the tile-sorted position
     const uint32_t lane_bit = 1u << lane;
@@ -500,8 +503,6 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         const uint32_t nv = (n - nb) < (size_t)(THREADS * ITEMS) ? (uint32_t)(n - nb) : (uint32_t)(THREADS * ITEMS);
         load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, nb, nv);
     }
-
-    PHASE_MARK(4);
     // ---- decoupled look-back (thread d), then the global - local offset of every bin.
     // Under load a status read takes ~2.5 us (it queues behind the SM's own bulk traffic) and a
     // tile finishes every ~55 ns, so ~35 predecessors have no inclusive prefix yet when a tile
@@ -561,9 +562,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         s_off[tid] = gbase - bin_start;
         if (base_out != nullptr && last_tile) base_out[tid] = gbase + count;
     }
-    PHASE_MARK(5);
     __syncthreads();
-    PHASE_MARK(6);
 
     // ---- read-out: consecutive threads take consecutive tile-sorted slots -> coalesced runs
 #pragma unroll
@@ -598,7 +597,6 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
         for (int i = tid; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
     __syncthreads();
-    PHASE_MARK(7);
     return next_tile;
 }
 
@@ -688,9 +686,11 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     uint32_t p_tile = 0, p_count = 0, p_bin_start = 0;
     uint32_t lb_v[GROUP_TILES - 1], lb_ga[GROUP_LOOK], lb_gq[GROUP_LOOK];
     uint32_t iter = 0;
+    PHASE_BEGIN();
     while (true) {
         const bool cur = tile < full_tiles; // block-uniform
         if (!cur && !have_prev) break;
+        PHASE_MARK(8); // issue of the look-back loads and the key prefetch (waits for phase C's stores to drain)
         const size_t tile_base = (size_t)tile * TILE;
         uint32_t count = 0;
         bool warp_one_digit = false;
@@ -699,6 +699,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (cur) {
             // ticket of the tile after this one (slot alternates: it is read a full iteration later)
             if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
+#ifdef THRS_PHASE_TIMING
+            if (tid == 0 && s_misc[12 + (iter & 1u)] < 32768u) g_trace[0][s_misc[12 + (iter & 1u)]] = trace_now();
+#endif
             // ---- phase A(tile): per-warp digit counts; and does this warp hold ONE digit only?
             // (all-equal keys, zero high bytes, sorted input: the ranking atomics would serialise
             // 32-way on one counter, while the positions are simply consecutive)
@@ -722,7 +725,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 for (int j = 0; j < ITEMS; ++j) val[j] = vin[j * 32];
             }
         }
+        PHASE_MARK(9);
         __syncthreads();
+        PHASE_MARK(10);
 
         // ---- scan(tile): thread d owns digit d
         if (cur && tid < RADIX) {
@@ -730,6 +735,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
             for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
             st_relaxed(status + (size_t)tile * RADIX + tid, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
             atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
+            TRACE(1, tile);
         }
         const uint32_t bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
         if (cur && tid < RADIX) {
@@ -742,10 +748,12 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 run += c;
             }
         }
+        PHASE_MARK(11);
 
         // ---- resolve(prev): the look-back loads were issued at the end of the previous iteration
         if (have_prev && tid < RADIX) {
             uint32_t excl = 0;
+            TRACE(4, p_tile);
             if (p_tile != 0) {
                 const uint32_t g = p_tile / GROUP_TILES, r = p_tile % GROUP_TILES;
                 const uint32_t* col = status + tid;
@@ -756,11 +764,16 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 for (int i = 0; i < GROUP_TILES - 1; ++i) {
                     if ((uint32_t)i < r && !done) {
                         uint32_t sv = lb_v[i];
-                        while ((sv >> FLAG_SHIFT) == 0u) sv = ld_relaxed(col + (size_t)(p_tile - 1 - i) * RADIX);
+                        while ((sv >> FLAG_SHIFT) == 0u) {
+                            sv = ld_relaxed(col + (size_t)(p_tile - 1 - i) * RADIX);
+                            LB_COUNT(1);
+                        }
                         excl += sv & VALUE_MASK;
                         done = (sv >> FLAG_SHIFT) == 2u;
                     }
                 }
+                LB_COUNT(0);
+                if (done) LB_COUNT(3);
                 if (!done) {
                     // excl = counts of the group's earlier tiles; add the prefix through group g-1
                     uint32_t pg = 0, gg = g;
@@ -773,6 +786,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                         }
                     }
                     while (!have) { // beyond the prefetched rows, or a group still filling: poll
+                        LB_COUNT(4);
                         const uint32_t q = gg == 0u ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
                         if ((q >> FLAG_SHIFT) == 2u) { pg += q & VALUE_MASK; have = true; break; }
                         const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
@@ -783,6 +797,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 }
                 st_relaxed(status + (size_t)p_tile * RADIX + tid, FLAG_PREFIX | (excl + p_count));
             }
+            TRACE(5, p_tile);
             const uint32_t gbase = base_in[tid] + excl;
             s_off[tid] = gbase - p_bin_start;
             if (base_out != nullptr && p_tile == num_tiles - 1) base_out[tid] = gbase + p_count;
@@ -791,7 +806,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 s_run[8 + tid] = p_count;
             }
         }
+        PHASE_MARK(12);
         __syncthreads();
+        PHASE_MARK(13);
 
         // ---- read-out(prev)
         if (PEER && have_prev) {
@@ -845,7 +862,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 }
             }
         }
+        PHASE_MARK(14);
         __syncthreads();
+        PHASE_MARK(15);
         if (!cur) break;
 
         // ---- phase C(tile): rank and stage at the tile-sorted position
@@ -903,8 +922,10 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
             for (int i = lane; i < ROW / 4; i += 32) z[i] = make_uint4(0u, 0u, 0u, 0u);
         }
         __syncwarp();
+        PHASE_MARK(7);
 
         // ---- look-back loads of this tile (consumed next iteration), then the next tile's keys
+        TRACE(2, tile); TRACE(3, tile);
         if (tid < RADIX && tile != 0) {
             const uint32_t g = tile / GROUP_TILES, r = tile % GROUP_TILES;
 #pragma unroll
