@@ -201,6 +201,15 @@ THRS_API int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in
 #define THRS_SMALL_SORT_MAX 4096u
 THRS_API int thrs_set_small_path(thrs_sorter* s, int enabled);
 
+/* Inputs of at most THRS_MID_SORT_MAX items (and more than THRS_SMALL_SORT_MAX) run the same
+ * histogram + onesweep launches with a quarter-size tile (4 096 items for 4-byte keys), so that a
+ * 2^20-key pass is 256 short tiles over all SMs instead of 64 long ones.  thrs_set_mid_max lowers the
+ * limit (0 = always the full-size shape; values above THRS_MID_SORT_MAX are clamped to it, because
+ * thrs_temp_bytes sizes the look-back rows for that limit).  Tests use it to run both shapes on the
+ * same inputs. */
+#define THRS_MID_SORT_MAX (1u << 20)
+THRS_API int thrs_set_mid_max(thrs_sorter* s, uint32_t max_items);
+
 /* Diagnostics. */
 THRS_API const char* thrs_last_error(void);        /* thread-local text of the last failure */
 THRS_API const char* thrs_version(void);

@@ -82,6 +82,7 @@ int main(int argc, char** argv)
     thrs_temp_def def; thrs_temp_bytes(s, n, &def);
     void* temp; CK(cudaMalloc(&temp, def.pSumBuffer + def.keyOutBuffer + (pairs ? def.valueOutBuffer : 0)));
     if (getenv("THRS_RANKING")) thrs_set_ranking(s, atoi(getenv("THRS_RANKING")));
+    if (getenv("THRS_MID_MAX")) thrs_set_mid_max(s, (uint32_t)strtoull(getenv("THRS_MID_MAX"), 0, 10));
     { int r = 0, ok = 0; uint64_t g = 0; thrs_get_ranking(s, &r, &ok, &g); printf("[ranking %s, probe %s, %llu groups] ", r == 2 ? "counter-return" : "match-mask", ok ? "in order" : "OUT OF ORDER", (unsigned long long)g); }
     thrs_profile_enable(s, 1);
     thrs_profile best; best.total_ms = 1e9f;

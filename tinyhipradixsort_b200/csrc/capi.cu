@@ -62,6 +62,7 @@ struct thrs_sorter {
     int ranking_request = THRS_RANKING_AUTO;
     int fast = 0;
     int force_multiblock = 0; // tests: run small inputs through the histogram + onesweep path too
+    uint32_t mid_max = THRS_MID_SORT_MAX; // n <= mid_max sorts with the quarter-size tile shape
     int probe_in_order = 0;
     unsigned long long probe_groups = 0;
     // workspace of thrs_sort_host (grown on demand, guarded)
@@ -137,14 +138,19 @@ int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out)
     // One layout serves sortKeys and sortPairs of this sorter: size the status rows for
     // the smaller of the two tile shapes.  Pure, monotone function of n (hpp:859).
     // ... and of both rankings, so the size does not depend on what the device probe decides.
-    uint32_t t_min = 0xffffffffu;
+    uint32_t t_min = 0xffffffffu, t_mid = 0xffffffffu;
     for (int f = 0; f < 2; ++f) {
         const uint32_t t_keys = s->table->tile_items[f][0];
         const uint32_t t_pairs = s->table->tile_items[f][s->vslot];
         if (t_keys < t_min) t_min = t_keys;
         if (t_pairs < t_min) t_min = t_pairs;
     }
-    const uint64_t tiles = div_up(n, t_min);
+    t_mid = s->table->tile_items_mid[0] < s->table->tile_items_mid[s->vslot] ? s->table->tile_items_mid[0]
+                                                                             : s->table->tile_items_mid[s->vslot];
+    // the quarter-size shape is only ever used up to THRS_MID_SORT_MAX items (thrs_set_mid_max clamps)
+    const uint64_t tiles_big = div_up(n, t_min);
+    const uint64_t tiles_mid = div_up(n < THRS_MID_SORT_MAX ? n : THRS_MID_SORT_MAX, t_mid);
+    const uint64_t tiles = tiles_big > tiles_mid ? tiles_big : tiles_mid;
     const uint64_t passes = (uint64_t)s->kbytes; // key bits / 8
     out->pSumBuffer = align16(4ull * (Scratch::CONTROL_WORDS + passes * Scratch::pass_words(tiles)));
     out->keyOutBuffer = align16((uint64_t)s->kbytes * n);
@@ -162,6 +168,7 @@ static int prepare_device(thrs_sorter* s)
         for (int f = 0; f < 2; ++f)
             for (int v = 0; v < 4 && e == cudaSuccess; ++v) {
                 e = s->table->prepare[f][v]();
+                if (e == cudaSuccess) e = s->table->prepare_mid[f][v]();
                 if (e == cudaSuccess && s->table->prepare_scatter[f][v]) e = s->table->prepare_scatter[f][v]();
             }
         for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare_small[v]();
@@ -250,7 +257,8 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     char* key_out = static_cast<char*>(temp) + def.pSumBuffer;
     char* val_out = key_out + def.keyOutBuffer;
 
-    const uint32_t tile = s->table->tile_items[s->fast][vslot];
+    const bool mid = n <= s->mid_max;
+    const uint32_t tile = mid ? s->table->tile_items_mid[vslot] : s->table->tile_items[s->fast][vslot];
     const uint64_t tiles_total = div_up(n, tile);
     const uint64_t part_items = (uint64_t)(VALUE_MASK / tile) * tile; // < 2^30, whole tiles
     const int parts = (int)div_up(n, part_items);
@@ -299,7 +307,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
             a.sm_count = s->sm_count;
             a.base_in = sc.base(p, q);
             a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;
-            CUDA_TRY(s->table->onesweep[s->fast][vslot](a, stream), "onesweep_kernel launch");
+            CUDA_TRY((mid ? s->table->onesweep_mid : s->table->onesweep)[s->fast][vslot](a, stream), "onesweep_kernel launch");
             ++g_launches;
         }
         CUDA_TRY(mark(), "profile event");
@@ -536,6 +544,13 @@ int thrs_set_small_path(thrs_sorter* s, int enabled)
 {
     if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_small_path: NULL sorter");
     s->force_multiblock = enabled ? 0 : 1;
+    return THRS_OK;
+}
+
+int thrs_set_mid_max(thrs_sorter* s, uint32_t max_items)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_mid_max: NULL sorter");
+    s->mid_max = max_items < THRS_MID_SORT_MAX ? max_items : THRS_MID_SORT_MAX; // the temp layout covers no more
     return THRS_OK;
 }
 

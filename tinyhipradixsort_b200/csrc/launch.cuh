@@ -44,6 +44,15 @@ template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 
 template <bool FAST> struct Tuning<8, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
 #endif
 
+// Mid-size inputs (n <= THRS_MID_SORT_MAX, capi.cu): a quarter-size tile.  With the full-size shape a
+// 2^20-key pass is 64 tiles on 148 SMs and lasts one whole tile lifetime (~12 us); 256 tiles of 4 096
+// keep every SM busy and a tile's barrier-to-barrier chain is four times shorter.
+template <int KBYTES, int VBYTES> struct MidTuning {
+    static constexpr int THREADS = 256, ITEMS = (KBYTES + VBYTES <= 8) ? 16 : 8, MINB = 2;
+};
+template <int KBYTES, int VBYTES, bool FAST, bool MID> struct ShapeOf { using type = Tuning<KBYTES, VBYTES, FAST>; };
+template <int KBYTES, int VBYTES, bool FAST> struct ShapeOf<KBYTES, VBYTES, FAST, true> { using type = MidTuning<KBYTES, VBYTES>; };
+
 struct OnesweepArgs {
     const void* keys_in;
     void* keys_out;
@@ -73,6 +82,10 @@ struct KernelTable {
     cudaError_t (*prepare[2][4])(); // opt in to > 48 KiB dynamic shared memory
     cudaError_t (*prepare_histogram)();
     uint32_t tile_items[2][4];
+    // quarter-size tile shape for mid-size inputs (MidTuning); same index meaning
+    cudaError_t (*onesweep_mid[2][4])(const OnesweepArgs& a, cudaStream_t stream);
+    cudaError_t (*prepare_mid[2][4])();
+    uint32_t tile_items_mid[4];
     // scatter pass (per-digit destination pointers); 4- and 8-byte values only, else nullptr
     cudaError_t (*scatter[2][4])(const OnesweepArgs& a, cudaStream_t stream);
     cudaError_t (*prepare_scatter[2][4])();
@@ -134,10 +147,10 @@ cudaError_t prepare_histogram()
     return e;
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false>
 cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
 {
-    using T = Tuning<(int)sizeof(KeyT), VBYTES, FAST>;
+    using T = typename ShapeOf<(int)sizeof(KeyT), VBYTES, FAST, MID>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
     using ValT = typename ValueOf<VBYTES>::type;
     const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
@@ -151,15 +164,16 @@ cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false>
 cudaError_t prepare_onesweep()
 {
-    using T = Tuning<(int)sizeof(KeyT), VBYTES, FAST>;
+    using T = typename ShapeOf<(int)sizeof(KeyT), VBYTES, FAST, MID>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
     return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER>,
                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES);
 }
 
+template <int KB, int VB> constexpr uint32_t mid_tile_of() { return (uint32_t)(MidTuning<KB, VB>::THREADS * MidTuning<KB, VB>::ITEMS); }
 template <int KB, int VB, bool FAST> constexpr uint32_t tile_of() { return (uint32_t)(Tuning<KB, VB, FAST>::THREADS * Tuning<KB, VB, FAST>::ITEMS); }
 
 template <class KeyT, int KIND, bool DESC>
@@ -179,6 +193,15 @@ const KernelTable* make_table()
         &prepare_histogram<KeyT, KIND, DESC>,
         {{tile_of<KB, 0, false>(), tile_of<KB, 4, false>(), tile_of<KB, 8, false>(), tile_of<KB, 16, false>()},
          {tile_of<KB, 0, true>(), tile_of<KB, 4, true>(), tile_of<KB, 8, true>(), tile_of<KB, 16, true>()}},
+        {{&launch_onesweep<KeyT, KIND, DESC, 0, false, false, true>, &launch_onesweep<KeyT, KIND, DESC, 4, false, false, true>,
+          &launch_onesweep<KeyT, KIND, DESC, 8, false, false, true>, &launch_onesweep<KeyT, KIND, DESC, 16, false, false, true>},
+         {&launch_onesweep<KeyT, KIND, DESC, 0, true, false, true>, &launch_onesweep<KeyT, KIND, DESC, 4, true, false, true>,
+          &launch_onesweep<KeyT, KIND, DESC, 8, true, false, true>, &launch_onesweep<KeyT, KIND, DESC, 16, true, false, true>}},
+        {{&prepare_onesweep<KeyT, KIND, DESC, 0, false, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 4, false, false, true>,
+          &prepare_onesweep<KeyT, KIND, DESC, 8, false, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 16, false, false, true>},
+         {&prepare_onesweep<KeyT, KIND, DESC, 0, true, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 4, true, false, true>,
+          &prepare_onesweep<KeyT, KIND, DESC, 8, true, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 16, true, false, true>}},
+        {mid_tile_of<KB, 0>(), mid_tile_of<KB, 4>(), mid_tile_of<KB, 8>(), mid_tile_of<KB, 16>()},
         {{nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, false, true>, &launch_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},
          {nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, true, true>, &launch_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}},
         {{nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},

@@ -277,6 +277,12 @@ class RadixSort:
         """Enable/disable the one-block path for n <= SMALL_SORT_MAX (thrs_set_small_path)."""
         _check(self._lib.thrs_set_small_path(self._h, int(bool(enabled))))
 
+    MID_SORT_MAX = 1 << 20
+
+    def setMidMax(self, maxItems):
+        """Largest n sorted with the quarter-size tile shape (thrs_set_mid_max); 0 = full-size tiles only."""
+        _check(self._lib.thrs_set_mid_max(self._h, int(maxItems)))
+
     RANKING_AUTO, RANKING_MATCH_MASK, RANKING_COUNTER_RETURN = 0, 1, 2
 
     def setRanking(self, ranking):
