@@ -7,6 +7,7 @@
 // pass (+ an async copy-back when the pass count is odd) instead of 3 launches per pass.
 // Calls the CUDA runtime directly: no Orochi, no NVRTC, no CPU fallback.
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <mutex>
 #include <new>
 #include <stdio.h>
@@ -62,6 +63,7 @@ struct thrs_sorter {
     int ranking_request = THRS_RANKING_AUTO;
     int fast = 0;
     int force_multiblock = 0; // tests: run small inputs through the histogram + onesweep path too
+    int pdl = 1; // programmatic dependent launch between the launches of one sort (THRS_PDL=0 disables: dev A/B)
     uint32_t mid_max = THRS_MID_SORT_MAX; // n <= mid_max sorts with the quarter-size tile shape
     int probe_in_order = 0;
     unsigned long long probe_groups = 0;
@@ -114,6 +116,7 @@ int thrs_create(const thrs_config* cfg, thrs_sorter** out)
     s->kbytes = key_bytes(cfg->key_type);
     s->vbytes = value_bytes(cfg->value_type);
     s->vslot = value_slot(cfg->value_type);
+    if (const char* e = getenv("THRS_PDL")) s->pdl = atoi(e) != 0; // dev A/B switch only
     *out = s;
     return THRS_OK;
 }
@@ -307,6 +310,9 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
             a.sm_count = s->sm_count;
             a.base_in = sc.base(p, q);
             a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;
+            // the launch before this one on the stream is the histogram or a onesweep launch, unless
+            // a profiling event was recorded in between
+            a.pdl = s->pdl && !s->profiling;
             CUDA_TRY((mid ? s->table->onesweep_mid : s->table->onesweep)[s->fast][vslot](a, stream), "onesweep_kernel launch");
             ++g_launches;
         }

@@ -115,6 +115,14 @@ __device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Programmatic dependent launch (sort_impl launches every pass with
+// cudaLaunchAttributeProgrammaticStreamSerialization): a kernel lets its successor's blocks be
+// scheduled right away, and the successor does everything that does not depend on its predecessor's
+// output (shared-memory set-up, its first ticket) before it waits for the predecessor to complete
+// and flush.  Both instructions are no-ops in a launch without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------------------------------
 // Block-wide exclusive scan of one value per thread for the first 256 threads.
 // `s_warp` needs 8 words.  Must be called by every thread of the block.
@@ -179,6 +187,7 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     __shared__ uint32_t s_scan[8];
     __shared__ uint32_t s_last;
 
+    pdl_launch_dependents(); // pass 0's blocks may take their places; they wait for this grid to complete
     {
         uint4* z = reinterpret_cast<uint4*>(tab);
         const int nz = passes * RADIX * REP / 4;
@@ -656,6 +665,8 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
+    pdl_launch_dependents();
+    if (PEER) pdl_wait();
     if (PEER && tid < RADIX) { // visible after the first barrier below
         s_kptr[tid] = peer_keys[tid];
         s_vptr[tid] = PAIRS ? peer_vals[tid] : 0ull;
@@ -669,11 +680,13 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     const uint32_t num_tiles = (n + TILE - 1) / TILE;
     const uint32_t full_tiles = n / TILE;
 
+    // the ticket word was zeroed by the memset that precedes the histogram: safe before the wait
     if (tid == 0) s_misc[15] = atomicAdd(ticket, 1u);
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
         for (int i = tid; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
+    if (!PEER) pdl_wait(); // keys, values and bin bases of the previous launch are complete and visible from here
     __syncthreads();
     uint32_t tile = s_misc[15];
     KeyT key[ITEMS];

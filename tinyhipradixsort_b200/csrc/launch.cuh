@@ -71,6 +71,9 @@ struct OnesweepArgs {
     const unsigned long long* peer_keys = nullptr;
     const unsigned long long* peer_vals = nullptr;
     BinThresholds thresholds = {{256u, 256u, 256u, 256u, 256u, 256u, 256u}};
+    // programmatic dependent launch: this launch directly follows, on the same stream, the kernel
+    // that produced its inputs (the histogram or the previous pass)
+    bool pdl = false;
 };
 
 struct KernelTable {
@@ -157,11 +160,20 @@ cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
     // persistent blocks, T::MINB per SM; correctness does not depend on all of them being resident
     const uint32_t cap = (uint32_t)a.sm_count * T::MINB;
     const uint32_t grid = tiles < cap ? tiles : cap;
-    onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER><<<grid, T::THREADS, SM::BYTES, stream>>>(
-        static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out), static_cast<const ValT*>(a.vals_in),
-        static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status, a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out,
-        a.peer_keys, a.peer_vals, a.thresholds);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(T::THREADS);
+    cfg.dynamicSmemBytes = SM::BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = a.pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER>,
+                              static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out),
+                              static_cast<const ValT*>(a.vals_in), static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status,
+                              a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out, a.peer_keys, a.peer_vals, a.thresholds);
 }
 
 template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false>
