@@ -134,7 +134,7 @@ THRS_API int thrs_buffer_free(void* device_ptr);
  * While enabled, keep one sort in flight per sorter.  thrs_profile_read blocks until the
  * last profiled sort finished. */
 typedef struct thrs_profile {
-    float memset_ms;    /* scratch clear                      */
+    float memset_ms;    /* scratch clear (zero_kernel)        */
     float histogram_ms; /* histogram_kernel                   */
     float pass_ms[8];   /* onesweep_kernel launches of pass i */
     float copyback_ms;  /* odd pass count only                */
@@ -196,7 +196,7 @@ THRS_API int thrs_set_ranking(thrs_sorter* s, int ranking);
 THRS_API int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in_order, uint64_t* probe_groups);
 
 /* Inputs of at most THRS_SMALL_SORT_MAX items are sorted by ONE block in one launch (no scratch
- * traffic, no look-back); larger ones by 1 memset + 1 histogram + P onesweep launches.  The switch
+ * traffic, no look-back); larger ones by 1 zeroing + 1 histogram + P onesweep launches.  The switch
  * exists so tests can push small inputs through the multi-block path as well (default: enabled). */
 #define THRS_SMALL_SORT_MAX 4096u
 THRS_API int thrs_set_small_path(thrs_sorter* s, int enabled);

@@ -239,7 +239,7 @@ def test_keys_only_on_pair_sorter_and_streams():
     memcpy_d2d(out.data_ptr(), kb.data(), 4 * n)
     ek, _ = oracle.sort("u32", keys)
     assert np.array_equal(to_host(out, keys), ek)
-    assert sorter.lastLaunchCount() == 5  # 1 histogram + 4 onesweep passes
+    assert sorter.lastLaunchCount() == 6  # 1 zero + 1 histogram + 4 onesweep passes
 
 
 def test_two_sorts_in_flight_on_two_streams():

@@ -271,7 +271,9 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
 
     // zero: histograms, bases, tickets, counters and the status rows of the passes we run
     const size_t clear_bytes = 4ull * (Scratch::CONTROL_WORDS + (uint64_t)passes * Scratch::pass_words(tiles_total));
-    CUDA_TRY(cudaMemsetAsync(temp, 0, clear_bytes, stream), "cudaMemsetAsync(scratch)");
+    const bool pdl = s->pdl && !s->profiling;
+    CUDA_TRY(launch_zero(temp, clear_bytes, s->sm_count, stream), "zero_kernel launch");
+    ++g_launches;
     CUDA_TRY(mark(), "profile event");
 
     {
@@ -280,7 +282,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
         uint64_t grid = div_up(nvec > 0 ? nvec : 1, vec_per_block);
         const uint64_t cap = (uint64_t)s->sm_count; // one 1024-thread block (128 KiB table) per SM
         if (grid > cap) grid = cap;
-        CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bits, passes, sc, (int)grid, stream),
+        CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bits, passes, sc, (int)grid, stream, pdl),
                  "histogram_kernel launch");
         ++g_launches;
         CUDA_TRY(mark(), "profile event");
@@ -312,7 +314,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
             a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;
             // the launch before this one on the stream is the histogram or a onesweep launch, unless
             // a profiling event was recorded in between
-            a.pdl = s->pdl && !s->profiling;
+            a.pdl = pdl;
             CUDA_TRY((mid ? s->table->onesweep_mid : s->table->onesweep)[s->fast][vslot](a, stream), "onesweep_kernel launch");
             ++g_launches;
         }
@@ -361,7 +363,7 @@ int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, int start
         const uint64_t nvec = (uint64_t)n * s->kbytes / 16;
         uint64_t grid = div_up(nvec > 0 ? nvec : 1, (uint64_t)HIST_THREADS * 4);
         if (grid > (uint64_t)s->sm_count) grid = s->sm_count;
-        CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bit, 1, sc, (int)grid, stream), "histogram_kernel launch");
+        CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bit, 1, sc, (int)grid, stream, false), "histogram_kernel launch");
     }
     CUDA_TRY(cudaMemcpyAsync(counts_out, sc.hist(), 4ull * RADIX, cudaMemcpyDeviceToDevice, stream), "copy histogram");
     return THRS_OK;

@@ -151,6 +151,38 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_
     return inc - v + add;
 }
 
+// 256-wide exclusive scans, one per group of 256 consecutive threads (group = tid / 256), all groups at
+// once.  `s_warp` needs blockDim.x / 32 words.  Must be called by every thread of the block.
+__device__ __forceinline__ uint32_t group_exclusive_scan_256(uint32_t v, uint32_t* s_warp)
+{
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t add = 0;
+    const int w0 = warp & ~7;
+#pragma unroll
+    for (int w = 0; w < 8; ++w)
+        if (w0 + w < warp) add += s_warp[w0 + w];
+    __syncthreads();
+    return inc - v + add;
+}
+
+constexpr int ZERO_THREADS = 256;
+static __global__ void __launch_bounds__(ZERO_THREADS) zero_kernel(uint4* __restrict__ p, size_t n16)
+{
+    pdl_launch_dependents(); // the histogram may start counting; it waits before it adds to global memory
+    const size_t stride = (size_t)gridDim.x * ZERO_THREADS;
+    for (size_t i = (size_t)blockIdx.x * ZERO_THREADS + threadIdx.x; i < n16; i += stride) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // ---------------------------------------------------------------------------------------
 // histogram_kernel — single read of the keys, all passes at once.
 // Replaces `passes` launches of blockCount (kernel.cu:73-103) and the bin-major part of
@@ -184,7 +216,7 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     constexpr int passes = PASSES;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* tab = reinterpret_cast<uint32_t*>(smem_raw); // [passes][256][REP]
-    __shared__ uint32_t s_scan[8];
+    __shared__ uint32_t s_scan[HIST_THREADS / 32];
     __shared__ uint32_t s_last;
 
     pdl_launch_dependents(); // pass 0's blocks may take their places; they wait for this grid to complete
@@ -247,6 +279,8 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     for (; v < nvec; v += stride) count_vec(__ldg(vkeys + v));
     __syncthreads();
 
+    // the scratch words are zero from here on (zero_kernel, when this launch is programmatically dependent)
+    pdl_wait();
     // fold the lane replicas (rotated start: conflict-free) and add to the global histogram
     uint32_t* g_hist = sc.hist();
     for (int r = threadIdx.x; r < passes * RADIX; r += HIST_THREADS) {
@@ -266,12 +300,15 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    for (int p = 0; p < passes; ++p) {
+    // 256 threads per pass, HIST_THREADS / 256 passes at a time (one global round trip, not one per pass)
+    constexpr int AT_ONCE = HIST_THREADS / RADIX;
+    for (int p0 = 0; p0 < passes; p0 += AT_ONCE) {
+        const int p = p0 + (int)(threadIdx.x / RADIX);
+        const uint32_t d = threadIdx.x % RADIX;
         uint32_t c = 0;
-        if (threadIdx.x < RADIX) c = ld_relaxed(&g_hist[p * RADIX + threadIdx.x]);
-        uint32_t ex = block_exclusive_scan_256(c, s_scan, nullptr);
-        if (threadIdx.x < RADIX) sc.base(p, 0)[threadIdx.x] = ex;
-        __syncthreads();
+        if (p < passes) c = ld_relaxed(&g_hist[p * RADIX + d]);
+        const uint32_t ex = group_exclusive_scan_256(c, s_scan);
+        if (p < passes) sc.base(p, 0)[d] = ex;
     }
 }
 

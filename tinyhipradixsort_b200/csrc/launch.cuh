@@ -78,8 +78,9 @@ struct OnesweepArgs {
 
 struct KernelTable {
     // value slot: 0 = keys only, 1 = 4-byte, 2 = 8-byte, 3 = 16-byte values
+    // pdl: the launch directly follows zero_kernel on the stream (programmatic dependent launch)
     cudaError_t (*histogram)(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
-                             cudaStream_t stream);
+                             cudaStream_t stream, bool pdl);
     // first index: 0 = match-mask ranking, 1 = counter-return ranking
     cudaError_t (*onesweep[2][4])(const OnesweepArgs& a, cudaStream_t stream);
     cudaError_t (*prepare[2][4])(); // opt in to > 48 KiB dynamic shared memory
@@ -98,30 +99,52 @@ struct KernelTable {
 };
 
 template <class KeyT, int KIND, bool DESC, int PASSES>
-cudaError_t launch_histogram_p(const void* keys, uint32_t n, uint32_t start_bit, Scratch sc, int grid, cudaStream_t stream)
+cudaError_t launch_histogram_p(const void* keys, uint32_t n, uint32_t start_bit, Scratch sc, int grid, cudaStream_t stream,
+                               bool pdl)
 {
-    histogram_kernel<KeyT, KIND, DESC, PASSES><<<grid, HIST_THREADS, HistShape<(int)sizeof(KeyT)>::BYTES, stream>>>(
-        static_cast<const KeyT*>(keys), n, start_bit, sc);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(HIST_THREADS);
+    cfg.dynamicSmemBytes = HistShape<(int)sizeof(KeyT)>::BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, histogram_kernel<KeyT, KIND, DESC, PASSES>, static_cast<const KeyT*>(keys), n, start_bit, sc);
+}
+
+// Zeroes the scratch words one sort uses (replaces cudaMemsetAsync: being a kernel, the histogram that
+// follows can be launched programmatically dependent on it and count keys while the words are cleared).
+static inline cudaError_t launch_zero(void* p, size_t bytes, int sm_count, cudaStream_t stream)
+{
+    const size_t n16 = bytes / 16; // callers pass multiples of 16 (Scratch sizes are whole 1 KiB rows)
+    size_t grid = (n16 + ZERO_THREADS * 4 - 1) / (ZERO_THREADS * 4);
+    const size_t cap = (size_t)sm_count * 8;
+    if (grid > cap) grid = cap;
+    if (grid == 0) grid = 1;
+    zero_kernel<<<(unsigned)grid, ZERO_THREADS, 0, stream>>>(static_cast<uint4*>(p), n16);
     return cudaGetLastError();
 }
 
 template <class KeyT, int KIND, bool DESC>
 cudaError_t launch_histogram(const void* keys, uint32_t n, uint32_t start_bit, int passes, Scratch sc, int grid,
-                             cudaStream_t stream)
+                             cudaStream_t stream, bool pdl)
 {
     switch (passes) {
-    case 1: return launch_histogram_p<KeyT, KIND, DESC, 1>(keys, n, start_bit, sc, grid, stream);
-    case 2: return launch_histogram_p<KeyT, KIND, DESC, 2>(keys, n, start_bit, sc, grid, stream);
-    case 3: return launch_histogram_p<KeyT, KIND, DESC, 3>(keys, n, start_bit, sc, grid, stream);
-    case 4: return launch_histogram_p<KeyT, KIND, DESC, 4>(keys, n, start_bit, sc, grid, stream);
+    case 1: return launch_histogram_p<KeyT, KIND, DESC, 1>(keys, n, start_bit, sc, grid, stream, pdl);
+    case 2: return launch_histogram_p<KeyT, KIND, DESC, 2>(keys, n, start_bit, sc, grid, stream, pdl);
+    case 3: return launch_histogram_p<KeyT, KIND, DESC, 3>(keys, n, start_bit, sc, grid, stream, pdl);
+    case 4: return launch_histogram_p<KeyT, KIND, DESC, 4>(keys, n, start_bit, sc, grid, stream, pdl);
     default: break;
     }
     if (sizeof(KeyT) == 8) {
         switch (passes) {
-        case 5: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 5 : 1>(keys, n, start_bit, sc, grid, stream);
-        case 6: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 6 : 1>(keys, n, start_bit, sc, grid, stream);
-        case 7: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 7 : 1>(keys, n, start_bit, sc, grid, stream);
-        case 8: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 8 : 1>(keys, n, start_bit, sc, grid, stream);
+        case 5: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 5 : 1>(keys, n, start_bit, sc, grid, stream, pdl);
+        case 6: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 6 : 1>(keys, n, start_bit, sc, grid, stream, pdl);
+        case 7: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 7 : 1>(keys, n, start_bit, sc, grid, stream, pdl);
+        case 8: return launch_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 8 : 1>(keys, n, start_bit, sc, grid, stream, pdl);
         default: break;
         }
     }
