@@ -201,6 +201,16 @@ THRS_API int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in
 #define THRS_SMALL_SORT_MAX 4096u
 THRS_API int thrs_set_small_path(thrs_sorter* s, int enabled);
 
+/* Inputs above THRS_SMALL_SORT_MAX and up to 8 x THRS_SMALL_SORT_MAX = 32 768 items are sorted by ONE
+ * launch of one thread-block cluster of 2, 4 or 8 blocks:
+ * every block keeps 4 096 items on chip for the whole sort, digit counts and items travel between
+ * the blocks through distributed shared memory, no scratch traffic, result in place.
+ * thrs_set_cluster_path(s, 0) sends such inputs through the multi-block path instead (tests run
+ * both; thrs_set_small_path(s, 0) disables both one-launch paths).  thrs_cluster_sort_max reports
+ * the largest n this sorter sorts that way on the current device (needs a device). */
+THRS_API int thrs_set_cluster_path(thrs_sorter* s, int enabled);
+THRS_API int thrs_cluster_sort_max(thrs_sorter* s, uint32_t* max_items);
+
 /* Inputs of at most THRS_MID_SORT_MAX items (and more than THRS_SMALL_SORT_MAX) run the same
  * histogram + onesweep launches with a quarter-size tile (4 096 items for 4-byte keys), so that a
  * 2^20-key pass is 256 short tiles over all SMs instead of 64 long ones.  thrs_set_mid_max lowers the

@@ -22,6 +22,7 @@ SIZES = (4097, 8192, 8193, 12289, 99999, 300001, (1 << 20) - 5)
 def test_mid_inputs_both_tile_shapes(key, vb, desc, mid):
     s = make_sorter(key, vb, desc)
     s.setMidMax(thrs.RadixSort.MID_SORT_MAX if mid else 0)
+    s.setClusterPath(False)  # the sizes up to 32 768 would otherwise take the one-cluster path
     rng = oracle.SplitMix64(77)
     for n in SIZES:
         keys = rng.randomize(key, n, mode=1)
@@ -33,6 +34,7 @@ def test_mid_inputs_both_tile_shapes(key, vb, desc, mid):
 def test_mid_shape_skewed_digits_and_windows(ranking):
     s = make_sorter("u32", 4)
     s.setRanking(ranking)
+    s.setClusterPath(False)
     rng = oracle.SplitMix64(9)
     n = 200003
     vals = np.arange(n, dtype=np.uint32)

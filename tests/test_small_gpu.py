@@ -37,7 +37,8 @@ def test_small_inputs_both_paths(key, vb, desc, small):
         if n >= 32:
             keys[::3] = keys[0]  # duplicates: stability is visible in the values
         check_against_oracle(key, keys, _values(n, vb), 0, KEY_BITS[key], desc, s)
-        expect_one = small and n <= thrs.RadixSort.SMALL_SORT_MAX
+        # one launch: one block up to SMALL_SORT_MAX, one cluster up to clusterSortMax()
+        expect_one = small and n <= max(thrs.RadixSort.SMALL_SORT_MAX, s.clusterSortMax())
         assert (s.lastLaunchCount() == 1) == expect_one, (n, s.lastLaunchCount())
 
 

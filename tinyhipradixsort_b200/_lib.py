@@ -83,6 +83,8 @@ SIGNATURES = {
     "thrs_mg_last_error": (ctypes.c_char_p, []),
     "thrs_set_small_path": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_set_mid_max": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint32]),
+    "thrs_set_cluster_path": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "thrs_cluster_sort_max": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint32)]),
     "thrs_set_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_get_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),
                                         ctypes.POINTER(ctypes.c_uint64)]),

@@ -63,6 +63,8 @@ struct thrs_sorter {
     int ranking_request = THRS_RANKING_AUTO;
     int fast = 0;
     int force_multiblock = 0; // tests: run small inputs through the histogram + onesweep path too
+    int cluster_path = 1;       // SMALL_SORT_MAX < n <= cluster_blocks x SMALL_SORT_MAX: one cluster launch
+    int cluster_blocks[4] = {}; // largest schedulable cluster per value slot (prepare_device)
     int pdl = 1; // programmatic dependent launch between the launches of one sort (THRS_PDL=0 disables: dev A/B)
     uint32_t mid_max = THRS_MID_SORT_MAX; // n <= mid_max sorts with the quarter-size tile shape
     int probe_in_order = 0;
@@ -116,7 +118,8 @@ int thrs_create(const thrs_config* cfg, thrs_sorter** out)
     s->kbytes = key_bytes(cfg->key_type);
     s->vbytes = value_bytes(cfg->value_type);
     s->vslot = value_slot(cfg->value_type);
-    if (const char* e = getenv("THRS_PDL")) s->pdl = atoi(e) != 0; // dev A/B switch only
+    if (const char* e = getenv("THRS_PDL")) s->pdl = atoi(e) != 0; // dev A/B switches only
+    if (const char* e = getenv("THRS_CLUSTER")) s->cluster_path = atoi(e) != 0;
     *out = s;
     return THRS_OK;
 }
@@ -175,6 +178,7 @@ static int prepare_device(thrs_sorter* s)
                 if (e == cudaSuccess && s->table->prepare_scatter[f][v]) e = s->table->prepare_scatter[f][v]();
             }
         for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare_small[v]();
+        for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare_cluster[v](&s->cluster_blocks[v]);
         if (e == cudaSuccess) e = s->table->prepare_histogram();
         // which ranking this device can run exactly (probe.cuh); once per process and device
         if (e == cudaSuccess) {
@@ -245,6 +249,22 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
     if (n <= SMALL_SORT_MAX && !s->force_multiblock) {
         for (int i = 0; i < 3; ++i) CUDA_TRY(mark(), "profile event");
         CUDA_TRY(s->table->small[vslot](keys, values, n, (uint32_t)start_bits, passes, stream), "small_sort_kernel launch");
+        ++g_launches;
+        CUDA_TRY(mark(), "profile event");
+        s->ev_count = ev_i;
+        s->ev_passes = 1;
+        s->ev_parts = 1;
+        s->ev_copyback = false;
+        return THRS_OK;
+    }
+
+    // up to 8 x 4 096 items: one launch of one thread-block cluster, in place, no scratch (cluster_sort.cuh)
+    if (s->cluster_path && !s->force_multiblock && (uint64_t)n <= (uint64_t)s->cluster_blocks[vslot] * SMALL_SORT_MAX) {
+        int blocks = 2;
+        while ((uint64_t)blocks * SMALL_SORT_MAX < n) blocks *= 2;
+        for (int i = 0; i < 3; ++i) CUDA_TRY(mark(), "profile event");
+        CUDA_TRY(s->table->cluster[vslot](keys, values, n, (uint32_t)start_bits, passes, blocks, stream),
+                 "cluster_sort_kernel launch");
         ++g_launches;
         CUDA_TRY(mark(), "profile event");
         s->ev_count = ev_i;
@@ -552,6 +572,22 @@ int thrs_set_small_path(thrs_sorter* s, int enabled)
 {
     if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_small_path: NULL sorter");
     s->force_multiblock = enabled ? 0 : 1;
+    return THRS_OK;
+}
+
+int thrs_set_cluster_path(thrs_sorter* s, int enabled)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_cluster_path: NULL sorter");
+    s->cluster_path = enabled ? 1 : 0;
+    return THRS_OK;
+}
+
+int thrs_cluster_sort_max(thrs_sorter* s, uint32_t* max_items)
+{
+    if (!s || !max_items) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_cluster_sort_max: NULL argument");
+    int rc = prepare_device(s);
+    if (rc) return rc;
+    *max_items = s->cluster_path ? (uint32_t)s->cluster_blocks[s->vslot] * SMALL_SORT_MAX : 0u;
     return THRS_OK;
 }
 

@@ -5,6 +5,7 @@
 #pragma once
 #include "kernels.cuh"
 #include "small_sort.cuh"
+#include "cluster_sort.cuh"
 
 namespace thrs_b200 {
 
@@ -96,6 +97,9 @@ struct KernelTable {
     // one-block sort for n <= SMALL_SORT_MAX (small_sort.cuh)
     cudaError_t (*small[4])(void* keys, void* vals, uint32_t n, uint32_t start_bit, int passes, cudaStream_t stream);
     cudaError_t (*prepare_small[4])();
+    // one-cluster sort for SMALL_SORT_MAX < n <= blocks x SMALL_SORT_MAX (cluster_sort.cuh)
+    cudaError_t (*cluster[4])(void* keys, void* vals, uint32_t n, uint32_t start_bit, int passes, int blocks, cudaStream_t stream);
+    cudaError_t (*prepare_cluster[4])(int* max_blocks);
 };
 
 template <class KeyT, int KIND, bool DESC, int PASSES>
@@ -244,7 +248,11 @@ const KernelTable* make_table()
         {&launch_small_sort<KeyT, KIND, DESC, 0>, &launch_small_sort<KeyT, KIND, DESC, 4>,
          &launch_small_sort<KeyT, KIND, DESC, 8>, &launch_small_sort<KeyT, KIND, DESC, 16>},
         {&prepare_small_sort<KeyT, KIND, DESC, 0>, &prepare_small_sort<KeyT, KIND, DESC, 4>,
-         &prepare_small_sort<KeyT, KIND, DESC, 8>, &prepare_small_sort<KeyT, KIND, DESC, 16>}};
+         &prepare_small_sort<KeyT, KIND, DESC, 8>, &prepare_small_sort<KeyT, KIND, DESC, 16>},
+        {&launch_cluster_sort<KeyT, KIND, DESC, 0>, &launch_cluster_sort<KeyT, KIND, DESC, 4>,
+         &launch_cluster_sort<KeyT, KIND, DESC, 8>, &launch_cluster_sort<KeyT, KIND, DESC, 16>},
+        {&prepare_cluster_sort<KeyT, KIND, DESC, 0>, &prepare_cluster_sort<KeyT, KIND, DESC, 4>,
+         &prepare_cluster_sort<KeyT, KIND, DESC, 8>, &prepare_cluster_sort<KeyT, KIND, DESC, 16>}};
     return &t;
 }
 

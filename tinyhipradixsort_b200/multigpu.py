@@ -354,7 +354,7 @@ def bench(args, dist, rank, world, dev, g):
     ds.sort_pairs(keys, vals)
     prof = ops.sorter.readProfile()
     ops.sorter.profile(False)
-    launches_per_step = 1 + 1 + 5  # top-digit histogram, scatter pass, local sort (histogram + 4)
+    launches_per_step = 1 + 1 + 6  # top-digit histogram, scatter pass, local sort (zero + histogram + 4)
 
     # end to end: pinned host slices in, sorted share out (H2D + sort + D2H inside the timed region)
     hk0, hv0 = keys0.cpu().pin_memory(), vals0.cpu().pin_memory()

@@ -277,6 +277,16 @@ class RadixSort:
         """Enable/disable the one-block path for n <= SMALL_SORT_MAX (thrs_set_small_path)."""
         _check(self._lib.thrs_set_small_path(self._h, int(bool(enabled))))
 
+    def setClusterPath(self, enabled):
+        """Enable/disable the one-cluster path for SMALL_SORT_MAX < n <= 8 x SMALL_SORT_MAX (thrs_set_cluster_path)."""
+        _check(self._lib.thrs_set_cluster_path(self._h, int(bool(enabled))))
+
+    def clusterSortMax(self):
+        """Largest n sorted by one cluster launch on this device (thrs_cluster_sort_max) — needs a device."""
+        m = ctypes.c_uint32(0)
+        _check(self._lib.thrs_cluster_sort_max(self._h, ctypes.byref(m)))
+        return int(m.value)
+
     MID_SORT_MAX = 1 << 20
 
     def setMidMax(self, maxItems):
