@@ -196,8 +196,9 @@ THRS_API int thrs_set_ranking(thrs_sorter* s, int ranking);
 THRS_API int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in_order, uint64_t* probe_groups);
 
 /* Inputs of at most THRS_SMALL_SORT_MAX items are sorted by ONE block in one launch (no scratch
- * traffic, no look-back); larger ones by 1 zeroing + 1 histogram + P onesweep launches.  The switch
- * exists so tests can push small inputs through the multi-block path as well (default: enabled). */
+ * traffic, no look-back); larger ones by one cluster launch (below) or by 1 zeroing + 1 histogram + P
+ * onesweep launches.  The switch exists so tests can push small inputs through the multi-block path
+ * as well (default: enabled; disabling it also disables the one-cluster path). */
 #define THRS_SMALL_SORT_MAX 4096u
 THRS_API int thrs_set_small_path(thrs_sorter* s, int enabled);
 
