@@ -48,13 +48,18 @@ def _peaks():
 
 
 def _traffic():
-    """dram bytes per onesweep launch from the committed ncu capture, or None."""
+    """(dram bytes per onesweep launch, where the number comes from).  The figure is STATIC: it is read
+    from the committed `ncu --set full` capture (profiles/ncu_summary.json), not measured by this run."""
     p = os.path.join(ROOT, "profiles", "ncu_summary.json")
     try:
         with open(p) as f:
-            return json.load(f).get("onesweep_dram_bytes_per_launch")
+            d = json.load(f)
+        return d.get("onesweep_dram_bytes_per_launch"), f"static: profiles/ncu_summary.json ({d.get('captured', 'round 1')}, ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one onesweep launch at C2)"
     except Exception:
-        return None
+        return None, "no committed ncu capture"
+
+
+NORTH_STAR_PEAK_GBS = 8000.0  # the ~8 TB/s BASELINE.json's north_star quotes; the measured copy peak is lower
 
 
 class ClockSampler:
@@ -168,14 +173,24 @@ def cpu_sample(log2n):
     return keys, vals
 
 
+def _build_oracle_only():
+    """The reference arm must not load the product: build (if missing) and use oracle/ alone."""
+    import subprocess
+
+    if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle.so")):
+        r = subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("building oracle/liboracle.so failed")
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU check path on the host cores, bounded sample."""
+    """--impl reference: the reference's CPU check path on the host cores, at the SAME config as our
+    arm (2^28 pairs per step by default; --cpu-log2n shrinks it for quick local runs)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    import __graft_entry__ as ge
-
-    ge.build(quiet=True, only_missing=True)
+    _build_oracle_only()
     import oracle
 
     # torchrun exports OMP_NUM_THREADS=1: count the cores this process may run on instead
@@ -188,20 +203,23 @@ def run_reference(args):
     keys0, vals0 = cpu_sample(log2n)
     n = keys0.shape[0]
     times = []
-    for i in range(args.warmup + args.steps):
+    # a few minutes at most: one full-size sort takes seconds on all host cores
+    steps = args.steps if log2n < 28 else min(args.steps, 10)
+    warmup = args.warmup if log2n < 28 else min(args.warmup, 1)
+    for i in range(warmup + steps):
         k, v = keys0.copy(), vals0.copy()
         t = oracle.time_stable_sort_pairs_u32(k, v, threads)
-        if i >= args.warmup:
+        if i >= warmup:
             times.append(t)
     total = sum(times)
     value = n * len(times) / total
-    sample = (f"2^{log2n} u32 key + u32 value pairs (same generator as the GPU workload), "
-              f"__gnu_parallel::stable_sort on pair<key,value> by key, {threads} threads")
+    sample = (f"2^{log2n} u32 key + u32 value pairs (same generator and size as the GPU workload), "
+              f"__gnu_parallel::stable_sort on pair<key,value> by key, {threads} threads, {len(times)} timed sorts")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
+        "steps": len(times), "warmup": warmup, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": f"C2 sample: stable sort of 2^{log2n} u32 key-value pairs on host cores",
+        "config": {"workload": f"C2: stable sort of 2^{log2n} uniform-random u32 key + u32 value pairs on host cores, bits [0,32)",
                    "n_per_step": n, "bits": [0, 32]},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -209,6 +227,130 @@ def run_reference(args):
     }
     print(json.dumps(line), flush=True)
     return 0
+
+
+def _gen_case(torch, name, n, dev):
+    """Inputs of SURVEY.md 8d's configs other than C2 (keys as int32 bit patterns, values = index)."""
+    idx = torch.arange(0, n, dtype=torch.int64, device=dev)
+    r = _mix_torch(torch, idx)
+    vals = (idx & 0xFFFFFFFF).to(torch.int32)
+    if name == "equal":
+        keys = torch.full((n,), 0xDEADBEEF - (1 << 32), dtype=torch.int32, device=dev)
+    elif name == "range16":
+        keys = (r & 0xFFFF).to(torch.int32)
+    elif name == "unique8":
+        t8 = torch.tensor([0xDEADBEEF, 0, 0xFFFFFFFF, 0x80000000, 0x00010000, 0x12345678, 0x00FF00FF, 0x7FFFFFFF],
+                          dtype=torch.int64, device=dev)
+        keys = t8[(r & 7)].to(torch.int32)
+    elif name == "f32_specials":
+        # raw 32 random bits as float patterns (NaN/Inf/denormals occur naturally) + a sprinkle of specials
+        k = r & 0xFFFFFFFF
+        sp = torch.tensor([0x00000000, 0x80000000, 0x7F800000, 0xFF800000, 0x7FC00000, 0xFFC00000, 0x7F800001,
+                           0xFF800001, 0x00000001, 0x80000001, 0x007FFFFF, 0x807FFFFF, 0x7F7FFFFF, 0xFF7FFFFF],
+                          dtype=torch.int64, device=dev)
+        k[::4096] = sp[(idx[::4096] >> 12) % sp.shape[0]]
+        keys = k.to(torch.int32)
+    else:  # uniform
+        keys = (r & 0xFFFFFFFF).to(torch.int32)
+    return keys, vals
+
+
+def extra_cases(torch, thrs, dev, peak, reps=5):
+    """Device-timed side cases: C1, C2 keys-only, C3 and the eight C4 cases.  Each is
+    checked on the device (sorted on the window; pairs: equal fields keep ascending values) and
+    reported as best-of-reps ms, algorithmic GB/s and the fraction of the measured copy peak."""
+    out = {}
+
+    def field(keys, kind, lo, hi):
+        k = keys.to(torch.int64) & 0xFFFFFFFF
+        if kind == "f32":
+            k = torch.where(((k << 1) & 0xFFFFFFFF) == 0, torch.zeros_like(k), k)
+            k = torch.where(k >= 0x80000000, k ^ 0xFFFFFFFF, k | 0x80000000)
+        return (k >> lo) & ((1 << (hi - lo)) - 1)
+
+    def run(tag, kind, gen, log2n, pairs, lo, hi):
+        n = 1 << log2n
+        keys0, vals0 = _gen_case(torch, gen, n, dev)
+        cfg = thrs.RadixSort.Config()
+        cfg = cfg.configureWithKeyPair(kind, 4) if pairs else cfg.configureWithKey(kind)
+        srt = thrs.RadixSort([], cfg)
+        d = srt.getTemporaryBufferBytes(n)
+        tmp = torch.empty(d.getTemporaryBufferBytesForSortPairs() if pairs else d.getTemporaryBufferBytesForSortKeys(),
+                          dtype=torch.uint8, device=dev)
+        keys, vals = torch.empty_like(keys0), torch.empty_like(vals0)
+        st = torch.cuda.current_stream()
+        best = None
+        for _ in range(reps + 2):
+            keys.copy_(keys0)
+            vals.copy_(vals0)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(st)
+            if pairs:
+                srt.sortPairs(keys, vals, n, tmp, lo, hi, st)
+            else:
+                srt.sortKeys(keys, n, tmp, lo, hi, st)
+            b.record(st)
+            b.synchronize()
+            ms = a.elapsed_time(b)
+            best = ms if best is None or ms < best else best
+        f = field(keys, kind, lo, hi)
+        ok = bool((f[1:] >= f[:-1]).all())
+        if pairs and ok:
+            v = vals.to(torch.int64) & 0xFFFFFFFF
+            ok = bool(((f[1:] > f[:-1]) | (v[1:] > v[:-1])).all())
+            # association: the key that travelled with value v is the generated key of index v
+            ok = ok and bool((keys0[v] == keys).all())
+        passes = (hi - lo) // 8
+        alg = n * 4 + passes * 2 * n * (8 if pairs else 4)
+        out[tag] = {"n": n, "pairs": pairs, "bits": [lo, hi], "ms": best, "gbs_algorithmic": alg / (best * 1e-3) / 1e9,
+                    "frac_of_measured_peak": alg / (best * 1e-3) / 1e9 / peak, "gkeys_per_s": n / (best * 1e-3) / 1e9,
+                    "verified": ok}
+        del keys, vals, keys0, vals0, tmp
+        torch.cuda.empty_cache()
+        return ok
+
+    ok = run("C1_2pow20_u32_keys", "u32", "uniform", 20, False, 0, 32)
+    ok &= run("C2_2pow28_u32_keys_only", "u32", "uniform", 28, False, 0, 32)
+    ok &= run("C3_2pow28_f32_pairs_specials", "f32", "f32_specials", 28, True, 0, 32)
+    for gen in ("equal", "range16", "unique8"):
+        for pairs in (False, True):
+            ok &= run(f"C4_2pow27_{gen}_{'pairs' if pairs else 'keys'}", "u32", gen, 27, pairs, 0, 32)
+    for pairs in (False, True):
+        ok &= run(f"C4_2pow27_window_8_24_{'pairs' if pairs else 'keys'}", "u32", "uniform", 27, pairs, 8, 24)
+    return out, bool(ok)
+
+
+def reference_gpu_leg(torch, dev, keys0, vals0, n, ours_keys, ours_vals):
+    """The reference's own GPU kernels (kernel.cu compiled unmodified into oracle/_ref/kernel_u32_v4_asc.cubin,
+    driven by oracle/ref_gpu.cu with the launch shapes of tinyhipradixsort.hpp:864-943) on the same
+    input and GPU, OUTSIDE our timed region: ms of one sort (best of 3, CUDA events) and a bit-for-bit
+    comparison with our result.  None where the cubins were not built (no /root/reference)."""
+    try:
+        import oracle
+
+        if not oracle.RefGpuSorter.available():
+            return None
+        ref = oracle.RefGpuSorter("u32", 4, False)
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": str(e)[:200]}
+    tmp = torch.empty(ref.temp_bytes(n, True), dtype=torch.uint8, device=dev)
+    k, v = torch.empty_like(keys0), torch.empty_like(vals0)
+    st = torch.cuda.current_stream()
+    best = None
+    for _ in range(3):
+        k.copy_(keys0)
+        v.copy_(vals0)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        ref.sort(k.data_ptr(), v.data_ptr(), n, tmp.data_ptr(), 0, 32, st.cuda_stream)
+        b.record(st)
+        b.synchronize()
+        ms = a.elapsed_time(b)
+        best = ms if best is None or ms < best else best
+    same = bool((k == ours_keys).all()) and bool((v == ours_vals).all())
+    return {"ms": best, "keys_per_s": n / (best * 1e-3), "kernel": "reference kernel.cu, unmodified, sm_100a cubin (oracle/_ref)",
+            "launches": 12, "launch_shapes": "tinyhipradixsort.hpp:864-943 (blockCount, prefixSumExclusiveInplace, reorderKeyPair per pass)",
+            "identical_to_ours": same}
 
 
 def run_ours(args):
@@ -236,7 +378,9 @@ def run_ours(args):
     if world > 1:
         from tinyhipradixsort_b200 import multigpu
 
-        return multigpu.bench(args, dist, rank, world, dev, globals())
+        g = dict(globals())
+        g["_traffic"] = lambda: _traffic()[0]
+        return multigpu.bench(args, dist, rank, world, dev, g)
 
     n = 1 << args.log2n
     keys0, vals0 = gen_pairs(torch, 0, n, dev)
@@ -280,6 +424,9 @@ def run_ours(args):
         step_ms.append(ms)
         launches += l
     torch.cuda.synchronize()
+    # the result of the LAST TIMED step (programmatic dependent launch chain) is what gets checked ...
+    verified = check_sorted_stable(torch, keys, vals)
+    ref_gpu = None if args.no_reference_gpu else reference_gpu_leg(torch, dev, keys0, vals0, n, keys, vals)
     sorter.profile(True)
     profiled_step()
     for _ in range(args.steps):
@@ -289,7 +436,12 @@ def run_ours(args):
     sorter.profile(False)
     torch.cuda.synchronize()
     clocks = sampler.stop()
-    verified = check_sorted_stable(torch, keys, vals)
+    # ... and so is the result of the last profiled step (events between the launches, no PDL)
+    verified = verified and check_sorted_stable(torch, keys, vals)
+    if ref_gpu and "identical_to_ours" in ref_gpu:
+        verified = verified and ref_gpu["identical_to_ours"]
+    ranking = sorter.getRanking()
+    rcheck = sorter.getRankingCheck()
 
     total_ms = sum(step_ms)
     value = n * args.steps / (total_ms * 1e-3)
@@ -314,16 +466,20 @@ def run_ours(args):
     e2e_ok = bool((hk[1:].to(torch.int64) & 0xFFFFFFFF >= hk[:-1].to(torch.int64) & 0xFFFFFFFF).all())
     e2e_value = n * len(e2e_times) / sum(e2e_times)
 
-    # ---- CPU baseline: the oracle's restatement of the reference's CPU check path ----
+    peak, peak_src = _peaks()
+    extra, extra_ok = ({}, True) if args.no_extra else extra_cases(torch, thrs, dev, peak)
+
+    # ---- CPU baseline: the oracle's restatement of the reference's CPU check path, at the full C2 size ----
     import oracle
 
     ck, cv = cpu_sample(args.cpu_log2n)
     cpu_s = oracle.time_stable_sort_pairs_u32(ck, cv, 1)
     cpu = {"value": ck.shape[0] / cpu_s, "unit": UNIT, "cores": 1, "kind": "port",
-           "sample": f"2^{args.cpu_log2n} pairs of the same generator, std::stable_sort on pair<u32,u32> by key "
-                     f"(unittest.cpp:358-377), 1 thread of {os.cpu_count()} host cores, {cpu_s:.2f} s"}
+           "sample": f"2^{args.cpu_log2n} pairs of the same generator ({'the full C2 workload, timed once' if args.cpu_log2n == args.log2n else 'a sample'}), "
+                     f"std::stable_sort on pair<u32,u32> by key (unittest.cpp:358-377), 1 thread of {os.cpu_count()} host cores, {cpu_s:.2f} s"}
+    del ck, cv
 
-    peak, peak_src = _peaks()
+    traffic, traffic_src = _traffic()
     bytes_per_launch = 2.0 * n * (KEY_BYTES + VALUE_BYTES)
     avg_pass_ms = sum(pass_ms) / len(pass_ms)
     achieved = bytes_per_launch / (avg_pass_ms * 1e-3) / 1e9
@@ -336,14 +492,21 @@ def run_ours(args):
                                "stable, bits [0,32), single B200",
                    "n_per_step": n, "bits": [0, 32], "passes": PASSES,
                    "l2": "inputs (2 GiB keys+values) are larger than L2; input restored outside the timed events",
+                   "extra": extra,
                    "timing": "CUDA events on the launching stream around each sort call, summed over steps (launches of one sort chained by programmatic dependent launch); roofline.avg_launch_ms from the same number of additional steps with events between the launches"},
-        "verified": bool(verified and e2e_ok),
+        "verified": bool(verified and e2e_ok and extra_ok),
         "roofline": {"bound": "hbm", "kernel": "onesweep_kernel (one 8-bit pass)", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": _traffic(), "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": peak_src, "frac_of_8TBs": achieved / NORTH_STAR_PEAK_GBS,
                      "bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_pass_ms,
                      "histogram_ms": sum(hist_ms) / len(hist_ms),
                      "whole_sort_algorithmic_gbs": job_bytes / (total_ms / args.steps * 1e-3) / 1e9,
-                     "whole_sort_frac": job_bytes / (total_ms / args.steps * 1e-3) / 1e9 / peak},
+                     "whole_sort_frac": job_bytes / (total_ms / args.steps * 1e-3) / 1e9 / peak,
+                     "whole_sort_frac_of_8TBs": job_bytes / (total_ms / args.steps * 1e-3) / 1e9 / NORTH_STAR_PEAK_GBS},
+        "reference_gpu": ref_gpu,
+        "ranking": {"in_use": "counter-return" if ranking[0] == thrs.RadixSort.RANKING_COUNTER_RETURN else "match-mask",
+                    "probe_in_order": ranking[1], "probe_groups": ranking[2], "production_check_ok": rcheck[0],
+                    "production_check_items": rcheck[1]},
         "cpu_baseline": cpu,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * (KEY_BYTES + VALUE_BYTES),
                 "d2h_bytes_per_step": n * (KEY_BYTES + VALUE_BYTES), "ms_per_step": 1e3 * sum(e2e_times) / len(e2e_times),
@@ -352,7 +515,7 @@ def run_ours(args):
         "clocks": clocks,
     }
     print(json.dumps(line), flush=True)
-    return 0 if verified and e2e_ok else 1
+    return 0 if verified and e2e_ok and extra_ok else 1
 
 
 def main():
@@ -363,7 +526,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log2n", type=int, default=28, help="items per step at N=1")
     ap.add_argument("--log2n-per-gpu", type=int, default=28, help="items per GPU at N>1")
-    ap.add_argument("--cpu-log2n", type=int, default=26, help="size of the bounded CPU sample")
+    ap.add_argument("--cpu-log2n", type=int, default=28, help="size of the CPU baseline sort (28 = the full C2 workload)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the device-timed side cases (config.extra)")
+    ap.add_argument("--no-reference-gpu", action="store_true", help="skip the reference's GPU kernels leg")
+    ap.add_argument("--log2n-total", type=int, default=0, help="N>1: total items over all GPUs (strong scaling, C5 = 32)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -58,7 +58,8 @@ typedef enum thrs_status {
     THRS_ERR_BIT_RANGE = 2,        /* (endBits - startBits) % 8 != 0 (hpp:856) or end < start */
     THRS_ERR_CUDA = 3,             /* a CUDA runtime call failed; see thrs_last_error() */
     THRS_ERR_NO_DEVICE = 4,        /* no sm_100 device / no CUDA driver: there is NO CPU fallback */
-    THRS_ERR_ALIGNMENT = 5         /* buffer not aligned to its element size */
+    THRS_ERR_ALIGNMENT = 5,        /* buffer not aligned to its element size */
+    THRS_ERR_VERIFY = 6            /* THRS_VERIFY=1 only: the two rankings disagreed on this sort */
 } thrs_status;
 
 /* thrs::RadixSort::Config, tinyhipradixsort.hpp:697-705. */
@@ -87,7 +88,14 @@ typedef struct thrs_sorter thrs_sorter; /* opaque; replaces the Shader/module he
 THRS_API void thrs_config_default(thrs_config* cfg);
 
 /* thrs::RadixSort::RadixSort(extraArgs, config), hpp:751-804.  Selects precompiled
- * sm_100a kernels for the (key, value, order) triple; nothing is JIT-compiled. */
+ * sm_100a kernels for the (key, value, order) triple; nothing is JIT-compiled.  Where the
+ * reference compiles its module, this call prepares the CURRENT device: shared-memory opt-ins,
+ * SM count, and the two ranking checks described at thrs_set_ranking (a few milliseconds of
+ * device work, cached per process).  A sort on the prepared device only enqueues work on the
+ * caller's stream (safe under stream capture); a sort issued while ANOTHER device is current
+ * prepares that device on its first call there, and that one call synchronises.  Without any
+ * usable device the sorter is still created (thrs_temp_bytes needs none) and every sort returns
+ * THRS_ERR_NO_DEVICE. */
 THRS_API int thrs_create(const thrs_config* cfg, thrs_sorter** out);
 THRS_API void thrs_destroy(thrs_sorter* s);
 
@@ -184,9 +192,19 @@ THRS_API const char* thrs_mg_last_error(void);
 /* Ranking used by the onesweep kernels (no counterpart in the reference, which has one scheme,
  * kernel.cu:293-345).  COUNTER_RETURN takes the old value of a returning shared-memory atomicAdd
  * as the stable rank; it is exact only where lanes that hit one counter in one warp instruction
- * are served in ascending lane order, which a device probe checks on first use.  AUTO (default)
- * = COUNTER_RETURN if the probe found no group out of order, else MATCH_MASK (order-free).
- * Both run on the GPU; neither is a fallback to the host. */
+ * are served in ascending lane order.  CUDA DOES NOT PROMISE THAT ORDER: it is a property of the
+ * hardware that this library measures instead of assuming, twice, when a sorter prepares a device:
+ *   1. an isolated probe kernel (1e9 lane groups over duplicate-heavy / same-bank / partial-warp
+ *      patterns, checked against ballot-built peer masks);
+ *   2. a production check: the sorter's REAL onesweep kernels (full tiles, two blocks per SM, staging
+ *      and read-out traffic in flight) sort a duplicate-heavy 2^21-2^22-item input, keys-only and
+ *      pairs, once with each ranking, and the results are compared byte for byte on the device.
+ * AUTO (default) = COUNTER_RETURN only if both found nothing out of order, else MATCH_MASK (order-free
+ * by construction).  Both rankings run on the GPU; neither is a fallback to the host.
+ * Environment: THRS_VERIFY=1 makes EVERY counter-return sort of every sorter created afterwards run a
+ * second time with MATCH_MASK on a private copy and compare on the device (blocking, 3x memory;
+ * THRS_ERR_VERIFY on a difference) — for soak runs.  THRS_FORCE_RANK_MISMATCH=1 makes check 2 report
+ * a difference (test hook for the fall-back path). */
 #define THRS_RANKING_AUTO 0
 #define THRS_RANKING_MATCH_MASK 1
 #define THRS_RANKING_COUNTER_RETURN 2
@@ -194,6 +212,10 @@ THRS_API int thrs_set_ranking(thrs_sorter* s, int ranking);
 /* ranking_in_use: THRS_RANKING_MATCH_MASK or _COUNTER_RETURN; probe_in_order: 1 if the device
  * probe passed; probe_groups: multi-lane groups the probe checked.  Needs a device. */
 THRS_API int thrs_get_ranking(thrs_sorter* s, int* ranking_in_use, int* probe_in_order, uint64_t* probe_groups);
+/* production_check_ok: 1 if check 2 above found the two rankings identical on this device (0 if it
+ * differed, was forced to differ, or was not run because check 1 already failed); items_compared:
+ * items sorted under both rankings.  Needs a device. */
+THRS_API int thrs_get_ranking_check(thrs_sorter* s, int* production_check_ok, uint64_t* items_compared);
 
 /* Inputs of at most THRS_SMALL_SORT_MAX items are sorted by ONE block in one launch (no scratch
  * traffic, no look-back); larger ones by one cluster launch (below) or by 1 zeroing + 1 histogram + P

@@ -30,6 +30,69 @@ def test_probe_and_default_choice():
         s.setRanking(7)
 
 
+def test_production_check_ran_and_decides():
+    """AUTO needs BOTH checks: the isolated probe and the production-kernel comparison (capi.cu
+    run_production_rank_check: the real kernels under both rankings on a duplicate-heavy input)."""
+    for key, vb in (("u32", 4), ("u64", 8), ("f32", 16)):
+        s = make_sorter(key, vb)
+        in_use, in_order, _ = s.getRanking()
+        ok, items = s.getRankingCheck()
+        if in_order:
+            assert items >= 2 * (1 << 21) + 2 * (1 << 19), "keys-only and pairs, both tile shapes"
+        assert in_use == (COUNTER_RETURN if (in_order and ok) else MATCH_MASK)
+
+
+def test_forced_mismatch_falls_back_to_match_mask():
+    """THRS_FORCE_RANK_MISMATCH=1 makes the production check report a difference: a fresh process
+    must then resolve AUTO to the order-free ranking and still sort exactly."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import numpy as np, sys\n"
+        "sys.path.insert(0, 'tests')\n"
+        "import tinyhipradixsort_b200 as thrs\n"
+        "from helpers import make_sorter, check_against_oracle\n"
+        "s = make_sorter('u32', 4)\n"
+        "in_use, in_order, _ = s.getRanking()\n"
+        "ok, items = s.getRankingCheck()\n"
+        "assert not ok, 'forced mismatch not seen'\n"
+        "assert in_use == thrs.RadixSort.RANKING_MATCH_MASK, in_use\n"
+        "n = 300001\n"
+        "keys = (np.arange(n, dtype=np.uint64) * 2654435761 % 16).astype(np.uint32) * 0x01010101\n"
+        "check_against_oracle('u32', keys, np.arange(n, dtype=np.uint32), 0, 32, False, s)\n"
+        "print('FALLBACK-OK')\n"
+    )
+    env = dict(os.environ, THRS_FORCE_RANK_MISMATCH="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "FALLBACK-OK" in out.stdout, out.stdout + out.stderr
+
+
+def test_verify_mode_repeats_every_sort():
+    """THRS_VERIFY=1: every counter-return sort is repeated with match-mask on a copy and compared."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import numpy as np, sys\n"
+        "sys.path.insert(0, 'tests')\n"
+        "from helpers import make_sorter, check_against_oracle\n"
+        "for key, vb in (('u32', 4), ('u32', None), ('u64', 8)):\n"
+        "    s = make_sorter(key, vb)\n"
+        "    for n in (5000, 40000, 300001, 1 << 21):\n"
+        "        dt = np.uint32 if key == 'u32' else np.uint64\n"
+        "        keys = (np.arange(n, dtype=np.uint64) * 2654435761 % 251).astype(dt) * dt(0x01000101)\n"
+        "        vals = None if vb is None else np.arange(n, dtype=np.uint32 if vb == 4 else np.uint64)\n"
+        "        check_against_oracle(key, keys, vals, 0, None, False, s)\n"
+        "print('VERIFY-OK')\n"
+    )
+    env = dict(os.environ, THRS_VERIFY="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0 and "VERIFY-OK" in out.stdout, out.stdout + out.stderr
+
+
 def _dup_heavy(n, kind, seed):
     r = oracle.splitmix64_at(np.arange(n, dtype=np.uint64) + np.uint64(seed * 7919))
     if kind == "equal":

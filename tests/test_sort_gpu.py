@@ -221,6 +221,36 @@ def test_temp_sized_for_larger_n_and_reuse():
         assert np.array_equal(to_host(dk, keys), ek) and np.array_equal(to_host(dv, vals), ev)
 
 
+def test_temp_reuse_with_stale_tickets():
+    """ADVICE r1 (PDL ordering): a temp buffer that served a SMALLER sort holds tile tickets below the
+    next sort's tile count.  Were a pass-0 block able to draw its first ticket before zero_kernel cleared
+    that word, two blocks would take the same tile.  Alternate small and large sorts on one dirty temp
+    (never refilled), keys-only and pairs, and check every result on the device."""
+    sorter = make_sorter("u32", 4)
+    t = sorter.tileItems()
+    n_big = 300 * t + 17
+    d = sorter.getTemporaryBufferBytes(n_big)
+    tmp = torch.empty(d.getTemporaryBufferBytesForSortPairs(), dtype=torch.uint8, device="cuda")
+    g = torch.Generator(device="cuda")
+    g.manual_seed(5)
+    for it in range(40):
+        n = (3 * t + 5, n_big, 40 * t, n_big, 1 << 20, n_big)[it % 6]
+        k0 = torch.randint(-(1 << 31), (1 << 31) - 1, (n,), dtype=torch.int64, device="cuda", generator=g).to(torch.int32)
+        k, v = k0.clone(), torch.arange(n, dtype=torch.int32, device="cuda")
+        if it % 2:
+            sorter.sortPairs(k, v, n, tmp, 0, 32)
+        else:
+            sorter.sortKeys(k, n, tmp, 0, 32)
+        torch.cuda.synchronize()
+        ku = k.to(torch.int64) & 0xFFFFFFFF
+        assert bool((ku[1:] >= ku[:-1]).all()), f"iteration {it}: not sorted"
+        if it % 2:
+            assert bool(((ku[1:] > ku[:-1]) | (v[1:] > v[:-1])).all()), f"iteration {it}: not stable"
+            assert bool((k0[v.to(torch.int64)] == k).all()), f"iteration {it}: key/value association lost"
+        else:
+            assert bool((torch.sort(k0.to(torch.int64) & 0xFFFFFFFF).values == ku).all()), f"iteration {it}: not a permutation"
+
+
 def test_keys_only_on_pair_sorter_and_streams():
     # one sorter object serves sortKeys and sortPairs, on a non-default stream, with thrs::Buffer
     sorter = make_sorter("u32", 4)
@@ -312,3 +342,37 @@ def test_cpp_harness_unittest_and_helloworld():
     r = subprocess.run([os.path.join(root, "harness", "unittest"), "32"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-1000:]
     assert "0 failed cases" in r.stdout
+
+
+# ---- the reference's big cases through the C++ drop-in header (harness/bench_large.cpp, harness/main.cpp) ----
+def _run_harness(args, timeout):
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([os.path.join(root, "harness", args[0])] + [str(a) for a in args[1:]], capture_output=True, text=True,
+                       timeout=timeout)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    return r.stdout
+
+
+def test_cpp_harness_bench_160m_keys_and_pairs():
+    # UTEST(OrochiRadixSort, bench) / benchKeyPair, thrs leg (unittest.cpp:490-685): 160 M keys / pairs,
+    # event-timed, fully verified against a host sort.  The program's default is the reference's 4 runs;
+    # 2 here keeps the suite bounded.
+    out = _run_harness(["bench_large", "bench", 2], 900)
+    assert out.count("thrs::RadixSort::sortKeys") == 2 and "0 failed cases" in out, out
+    out = _run_harness(["bench_large", "benchKeyPair", 2], 900)
+    assert out.count("thrs::RadixSort::sortPairs") == 2 and "0 failed cases" in out, out
+
+
+def test_cpp_harness_u32large():
+    # UTEST(SortKeys, u32Large) (unittest.cpp:688-717): n = 2^31 + 100 through the C++ header
+    out = _run_harness(["bench_large", "u32Large"], 1800)
+    assert "[  OK  ] u32Large" in out and "0 failed cases" in out, out
+
+
+def test_cpp_harness_main_soak_bounded():
+    # main.cpp:128-203 with a bounded iteration count: keys-only (getKeyBits-ordered host sort) and KEY_PAIR
+    out = _run_harness(["main", 2, 0], 900)
+    assert "2 iterations verified" in out, out
+    out = _run_harness(["main", 1, 1], 900)
+    assert "1 iterations verified" in out, out

@@ -88,6 +88,7 @@ SIGNATURES = {
     "thrs_set_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_get_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),
                                         ctypes.POINTER(ctypes.c_uint64)]),
+    "thrs_get_ranking_check": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_uint64)]),
 }
 
 _lib = None

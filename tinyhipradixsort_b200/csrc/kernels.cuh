@@ -18,6 +18,17 @@
 
 namespace thrs_b200 {
 
+// THRS_RANK1: single-atomic counter-return ranking in the pipelined loop.  The returning atomicAdd of
+// phase A is the ONLY per-item atomic: its old value (the item's rank among the warp's items with the
+// same digit) is kept in a register, 16 bits per item, and phase C adds the per-warp base with a plain
+// load instead of a second atomic.  0 = two atomics (count in phase A, rank in phase C).
+#ifndef THRS_RANK1
+#define THRS_RANK1 0
+#endif
+#ifndef THRS_RANK1_DEPTH
+#define THRS_RANK1_DEPTH 8
+#endif
+
 constexpr int RADIX = 256;
 constexpr int MAX_PASSES = 8; // 64-bit keys / 8 bits
 constexpr int MAX_PARTS = 8;  // a sort is cut in parts of < 2^30 items so look-back words stay 32-bit
@@ -219,7 +230,6 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
     __shared__ uint32_t s_scan[HIST_THREADS / 32];
     __shared__ uint32_t s_last;
 
-    pdl_launch_dependents(); // pass 0's blocks may take their places; they wait for this grid to complete
     {
         uint4* z = reinterpret_cast<uint4*>(tab);
         const int nz = passes * RADIX * REP / 4;
@@ -281,6 +291,11 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
 
     // the scratch words are zero from here on (zero_kernel, when this launch is programmatically dependent)
     pdl_wait();
+    // Only now may pass 0's blocks be scheduled: an onesweep block draws its first ticket BEFORE its own
+    // griddepcontrol.wait, so its existence has to imply that zero_kernel has completed and flushed.  Every
+    // block of this grid is past its wait when the last one gets here, and a later pass can only be
+    // scheduled after all blocks of the pass before it exist, so the implication holds along the chain.
+    pdl_launch_dependents();
     // fold the lane replicas (rotated start: conflict-free) and add to the global histogram
     uint32_t* g_hist = sc.hist();
     for (int r = threadIdx.x; r < passes * RADIX; r += HIST_THREADS) {
@@ -688,6 +703,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     constexpr bool PAIRS = VBYTES > 0;
     constexpr bool PACKED = sizeof(KeyT) == 4 && VBYTES == 4;
     constexpr int ROW = FAST ? RADIX : 2 * RADIX; // 32-bit words per warp row of the table
+    constexpr bool R1 = FAST && (THRS_RANK1 != 0);
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* tbl32 = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_TBL);
     uint2* s_kv = reinterpret_cast<uint2*>(smem_raw + SM::OFF_VAL);
@@ -717,7 +733,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     const uint32_t num_tiles = (n + TILE - 1) / TILE;
     const uint32_t full_tiles = n / TILE;
 
-    // the ticket word was zeroed by the memset that precedes the histogram: safe before the wait
+    // First ticket before the wait: safe because this block can only have been scheduled after every
+    // histogram block passed ITS griddepcontrol.wait on zero_kernel (histogram_kernel triggers its
+    // dependents after that wait), so the ticket word is zero and nobody clears it again.
     if (tid == 0) s_misc[15] = atomicAdd(ticket, 1u);
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
@@ -746,6 +764,8 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         bool warp_one_digit = false;
         uint32_t warp_digit = 0;
         ValT val[PAIRS ? ITEMS : 1];
+        uint32_t rk[R1 ? (ITEMS + 3) / 4 : 1]; // R1: rank of item j in byte (j & 3) of rk[j / 4]
+        bool warp_rank_wide = false;
         if (cur) {
             // ticket of the tile after this one (slot alternates: it is read a full iteration later)
             if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
@@ -759,17 +779,56 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
             const uint32_t x_first = __shfl_sync(0xffffffffu, shifted_key_bits<KIND, DESC>(key[0], bit), 0);
             const uint32_t d_first = PEER ? bin_or_digit<PEER, KIND, DESC>(key[0], bit, th) : (x_first & 0xFFu);
             uint32_t diff = 0;
+            if (R1) {
+                // sameness first (ALU only), then ONE returning atomic per item.  bit_s == bit, hidden from
+                // ptxas so that the 40 shifted keys of this loop are not kept alive for the loop below
+                uint32_t bit_s = bit;
+                asm volatile("" : "+r"(bit_s));
+                const uint32_t x_first_s = __shfl_sync(0xffffffffu, shifted_key_bits<KIND, DESC>(key[0], bit_s), 0);
 #pragma unroll
-            for (int j = 0; j < ITEMS; ++j) {
-                const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit, th);
-                diff |= shifted_key_bits<KIND, DESC>(key[j], bit) ^ x_first;
-                atomicAdd(tw32 + base_word(d), 1u);
+                for (int j = 0; j < ITEMS; ++j) diff |= shifted_key_bits<KIND, DESC>(key[j], bit_s) ^ x_first_s;
+                warp_one_digit = __all_sync(0xffffffffu, (diff & 0xFFu) == 0u);
+                warp_digit = d_first;
+                if (warp_one_digit) {
+                    if (lane == 0) atomicAdd(tw32 + d_first, (uint32_t)(32 * ITEMS)); // ranks are j*32 + lane
+                } else {
+                    uint32_t any_r = 0;
+                    uint32_t ring[THRS_RANK1_DEPTH];
+#pragma unroll
+                    for (int j = 0; j < ITEMS; ++j) {
+                        // at most THRS_RANK1_DEPTH atomics in flight: the digit of item j is made to depend on the
+                        // rank returned DEPTH items earlier (always < 2^31, so the term is 0); without it ptxas
+                        // computes all 40 addresses ahead and spills the look-back registers
+                        KeyT kj = key[j];
+                        if (j >= THRS_RANK1_DEPTH) kj = kj + (KeyT)(ring[j % THRS_RANK1_DEPTH] >> 31);
+                        const uint32_t d = bin_or_digit<PEER, KIND, DESC>(kj, bit, th);
+                        const uint32_t r = atomicAdd(tw32 + d, 1u); // old value = rank in (warp, digit), lane order (probe.cuh)
+                        __syncwarp();
+                        ring[j % THRS_RANK1_DEPTH] = r;
+                        any_r |= r;
+                        // low byte of r into byte (j & 3) of rk[j / 4]: one PRMT
+                        rk[j >> 2] = (j & 3) == 0 ? r : __byte_perm(rk[j >> 2], r, (j & 3) == 1 ? 0x3240u : (j & 3) == 2 ? 0x3410u : 0x4210u);
+                    }
+                    // a digit with more than 256 items in this warp (skewed input): its ranks do not fit a byte,
+                    // the warp ranks again in phase C with a second atomic on the base table
+                    warp_rank_wide = __any_sync(0xffffffffu, (any_r >> 8) != 0u);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < ITEMS; ++j) {
+                    const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit, th);
+                    diff |= shifted_key_bits<KIND, DESC>(key[j], bit) ^ x_first;
+                    atomicAdd(tw32 + base_word(d), 1u);
+#ifdef THRS_DBL_ATOMS // dev: marginal cost of one more random shared-memory atomic per item
+                    atomicAdd(tw32 + base_word(d), 0u);
+#endif
+                }
+                // PEER bins several digits together: equal digits are sufficient there, not necessary
+                const bool same = (diff & 0xFFu) == 0u;
+                warp_one_digit = __all_sync(0xffffffffu, same);
+                warp_digit = d_first;
             }
-            // PEER bins several digits together: equal digits are sufficient there, not necessary
-            const bool same = (diff & 0xFFu) == 0u;
-            warp_one_digit = __all_sync(0xffffffffu, same);
-            warp_digit = d_first;
-            if (PAIRS) {
+            if (PAIRS && !R1) {
                 const ValT* vin = vals_in + tile_base + my0;
 #pragma unroll
                 for (int j = 0; j < ITEMS; ++j) val[j] = vin[j * 32];
@@ -859,6 +918,13 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         PHASE_MARK(12);
         __syncthreads();
         PHASE_MARK(13);
+        if (R1 && PAIRS && cur) {
+            // values are requested here (the look-back registers of prev are dead now); their latency
+            // hides behind the read-out of prev
+            const ValT* vin = vals_in + tile_base + my0;
+#pragma unroll
+            for (int j = 0; j < ITEMS; ++j) val[j] = vin[j * 32];
+        }
 
         // ---- read-out(prev)
         if (PEER && have_prev) {
@@ -893,18 +959,32 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const uint32_t p = k * THREADS + tid;
                 if (PACKED) {
                     const uint2 kv = s_kv[p];
+#ifdef THRS_DBL_LDS // dev: marginal cost of one more conflict-free 64-bit shared load per item
+                    { uint32_t a2, b2; asm volatile("ld.volatile.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a2), "=r"(b2) : "r"((uint32_t)__cvta_generic_to_shared(s_kv + p)) : "memory"); }
+#endif
                     const uint32_t d = bin_or_digit<PEER, KIND, DESC>((KeyT)kv.x, bit, th);
                     const uint32_t dst = s_off[d] + p;
                     KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                     ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
                     ko[dst] = (KeyT)kv.x;
                     store32(vo + dst, kv.y);
+#ifdef THRS_DBL_STG // dev: marginal cost of one more global store per item (same line: no extra DRAM traffic)
+                    *reinterpret_cast<volatile KeyT*>(ko + dst) = (KeyT)kv.x;
+                    *reinterpret_cast<volatile KeyT*>(ko + dst) = (KeyT)kv.x;
+#endif
                 } else {
                     const KeyT kk = s_keys[p];
+#ifdef THRS_DBL_LDS
+                    { const KeyT k2 = *reinterpret_cast<volatile KeyT*>(s_keys + p); asm volatile("" ::"r"((uint32_t)k2)); }
+#endif
                     const uint32_t d = bin_or_digit<PEER, KIND, DESC>(kk, bit, th);
                     const uint32_t dst = s_off[d] + p;
                     KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                     ko[dst] = kk;
+#ifdef THRS_DBL_STG
+                    *reinterpret_cast<volatile KeyT*>(ko + dst) = kk;
+                    *reinterpret_cast<volatile KeyT*>(ko + dst) = kk;
+#endif
                     if (PAIRS) {
                         ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
                         vo[dst] = s_vals[p];
@@ -939,7 +1019,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 // bit_c == bit (second kernel parameter): keeps ptxas from holding phase A's temporaries
                 const uint32_t d = bin_or_digit<PEER, KIND, DESC>(key[j], bit_c, th);
                 uint32_t pos;
-                if (FAST) {
+                if (R1 && !warp_rank_wide) {
+                    pos = tw32[d] + __byte_perm(rk[j >> 2], 0u, 0x4440u + (j & 3));
+                } else if (FAST) {
                     pos = atomicAdd(tw32 + d, 1u); // old value = stable position (probe.cuh)
                     __syncwarp();
                 } else {
@@ -957,11 +1039,24 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                     __syncwarp();
                     pos = e.y + lower;
                 }
+#ifndef THRS_DBL_STAGE
                 if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
                 else {
                     s_keys[pos] = key[j];
                     if (PAIRS) s_vals[pos] = val[j];
                 }
+#else // dev: marginal cost of one more random staging store per item
+                if (!PACKED && PAIRS) s_vals[pos] = val[j];
+                if (PACKED) { // both stores volatile: a plain store followed by an identical one is removed as dead
+                    asm volatile("st.volatile.shared.v2.u32 [%0], {%1, %2};" ::"r"((uint32_t)__cvta_generic_to_shared(s_kv + pos)),
+                                 "r"((uint32_t)key[j]), "r"(val32(val[j])) : "memory");
+                    asm volatile("st.volatile.shared.v2.u32 [%0], {%1, %2};" ::"r"((uint32_t)__cvta_generic_to_shared(s_kv + pos)),
+                                 "r"((uint32_t)key[j]), "r"(val32(val[j])) : "memory");
+                } else {
+                    *reinterpret_cast<volatile KeyT*>(s_keys + pos) = key[j];
+                    *reinterpret_cast<volatile KeyT*>(s_keys + pos) = key[j];
+                }
+#endif
             }
         }
         // this warp's table row is private until the next scan: zero it for the next phase A

@@ -29,13 +29,15 @@ template <bool FAST> struct Tuning<4, 0, FAST> {
     static constexpr int THREADS = THRS_TUNE_K_THREADS, ITEMS = THRS_TUNE_K_ITEMS, MINB = THRS_TUNE_K_MINB;
 };
 #ifndef THRS_TUNE_OLD_SHAPES
-// bytes staged per item = K + V; two blocks of 256 threads per SM within 227 KiB and 128 registers
-template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 256, ITEMS = 32, MINB = 2; };
-template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 256, ITEMS = 20, MINB = 2; };
+// bytes staged per item = K + V; two blocks of 256 threads per SM within 228 KiB and 128 registers.
+// Match-mask cells are 8 bytes (16 KiB table instead of 8): those shapes stage one or two items less per
+// thread so that two blocks still fit (static_assert in launch_onesweep; the scatter variant adds 4 KiB).
+template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 32 : 30, MINB = 2; };
+template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 20 : 19, MINB = 2; };
 template <bool FAST> struct Tuning<8, 0, FAST> { static constexpr int THREADS = 256, ITEMS = 40, MINB = 2; };
-template <bool FAST> struct Tuning<8, 4, FAST> { static constexpr int THREADS = 256, ITEMS = 32, MINB = 2; };
-template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 256, ITEMS = 24, MINB = 2; };
-template <bool FAST> struct Tuning<8, 16, FAST> { static constexpr int THREADS = 256, ITEMS = 16, MINB = 2; };
+template <bool FAST> struct Tuning<8, 4, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 32 : 30, MINB = 2; };
+template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 24 : 22, MINB = 2; };
+template <bool FAST> struct Tuning<8, 16, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 16 : 15, MINB = 2; };
 #else
 template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 2; };
 template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 512, ITEMS = 8, MINB = 1; };
@@ -183,6 +185,8 @@ cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
     using T = typename ShapeOf<(int)sizeof(KeyT), VBYTES, FAST, MID>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
     using ValT = typename ValueOf<VBYTES>::type;
+    // MINB blocks must really fit one SM (228 KiB shared memory, 1 KiB reserved per block): the grid below assumes it
+    static_assert((size_t)T::MINB * (SM::BYTES + 1024) <= 233472, "tile shape does not fit MINB blocks per SM");
     const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
     // persistent blocks, T::MINB per SM; correctness does not depend on all of them being resident
     const uint32_t cap = (uint32_t)a.sm_count * T::MINB;

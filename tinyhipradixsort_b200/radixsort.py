@@ -305,6 +305,12 @@ class RadixSort:
         _check(self._lib.thrs_get_ranking(self._h, ctypes.byref(r), ctypes.byref(ok), ctypes.byref(g)))
         return r.value, bool(ok.value), int(g.value)
 
+    def getRankingCheck(self):
+        """(production check passed, items sorted under both rankings) — thrs_get_ranking_check."""
+        ok, items = ctypes.c_int(0), ctypes.c_uint64(0)
+        _check(self._lib.thrs_get_ranking_check(self._h, ctypes.byref(ok), ctypes.byref(items)))
+        return bool(ok.value), int(items.value)
+
     def tileItems(self):
         return int(self._lib.thrs_tile_items(self._h))
 
