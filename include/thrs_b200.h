@@ -153,6 +153,29 @@ typedef struct thrs_profile {
 THRS_API int thrs_profile_enable(thrs_sorter* s, int on);
 THRS_API int thrs_profile_read(thrs_sorter* s, thrs_profile* out);
 
+/* Segmented sort (no counterpart in the reference, which sorts one array per call, hpp:845-852):
+ * nseg independent, CONTIGUOUS segments of one array, segment i = items [seg_begin[i], seg_begin[i+1])
+ * of `keys` (and `values`); seg_begin is a HOST array of nseg + 1 ascending offsets (< 2^32, every
+ * segment < 2^30 items).  Every segment is sorted exactly as thrs_sort_keys / thrs_sort_pairs would
+ * sort it alone — stable, bits [start_bits, end_bits) — but each pass is ONE launch over all segments
+ * (per-segment bin bases, look-back chains that restart at every segment), so many short sorts cost
+ * one sort's launches.  Result in place; items outside [seg_begin[0], seg_begin[nseg]) are untouched.
+ * `temp`: thrs_segments_temp_bytes(s, seg_begin[nseg], nseg, with_values) bytes, 16-byte aligned.
+ * Asynchronous on `stream`.  The multi-GPU layer sorts the top-digit buckets a rank received with it.
+ * thrs_sort_segments_ex is the out-of-place form: it ping-pongs between (keys, values) and
+ * (alt_keys, alt_values) — arrays of the same extent — uses `scratch`
+ * (thrs_segments_scratch_bytes) for its tables, does NOT copy back, and reports in *result_in_alt
+ * where the sorted segments lie.  values / alt_values NULL = keys only. */
+THRS_API uint64_t thrs_segments_temp_bytes(const thrs_sorter* s, uint64_t n_total, uint32_t nseg, int with_values);
+THRS_API int thrs_sort_segments_keys(thrs_sorter* s, void* keys, const uint64_t* seg_begin, uint32_t nseg, void* temp,
+                                     int start_bits, int end_bits, void* stream);
+THRS_API int thrs_sort_segments_pairs(thrs_sorter* s, void* keys, void* values, const uint64_t* seg_begin, uint32_t nseg,
+                                      void* temp, int start_bits, int end_bits, void* stream);
+THRS_API uint64_t thrs_segments_scratch_bytes(const thrs_sorter* s, uint64_t n_total, uint32_t nseg);
+THRS_API int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_keys, void* alt_values, void* scratch,
+                                   uint64_t scratch_bytes, const uint64_t* seg_begin, uint32_t nseg, int start_bits,
+                                   int end_bits, void* stream, int* result_in_alt);
+
 /* Multi-GPU layer (no counterpart in the reference, single device: unittest.cpp:22,51).
  * thrs_scatter_pairs: ONE stable pass over the 8-bit digit at start_bit (in sort order, i.e. of
  * getKeyBits ^ order mask) that splits the input into nbins <= 8 destination bins: bin b takes the

@@ -7,8 +7,11 @@
 #endif
 namespace thrs_b200 {
 using T1 = Tuning<4, ONE_VB, true>;
-template __global__ void onesweep_kernel<uint32_t, 0, false, ONE_VB, T1::THREADS, T1::ITEMS, T1::MINB, true, false>(
+#ifndef ONE_SEG
+#define ONE_SEG false
+#endif
+template __global__ void onesweep_kernel<uint32_t, 0, false, ONE_VB, T1::THREADS, T1::ITEMS, T1::MINB, true, false, ONE_SEG>(
     const uint32_t*, uint32_t*, const ValueOf<ONE_VB>::type*, ValueOf<ONE_VB>::type*, uint32_t, uint32_t, uint32_t, uint32_t*,
     uint32_t*, uint32_t*, uint32_t*, const uint32_t*, uint32_t*, const unsigned long long*, const unsigned long long*,
-    const BinThresholds);
+    const BinThresholds, const uint32_t*);
 }

@@ -88,6 +88,15 @@ SIGNATURES = {
     "thrs_set_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_get_ranking": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),
                                         ctypes.POINTER(ctypes.c_uint64)]),
+    "thrs_segments_temp_bytes": (ctypes.c_uint64, [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int]),
+    "thrs_segments_scratch_bytes": (ctypes.c_uint64, [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32]),
+    "thrs_sort_segments_keys": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p,
+                                               ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
+    "thrs_sort_segments_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
+                                                ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
+    "thrs_sort_segments_ex": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int,
+                                             ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]),
     "thrs_get_ranking_check": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_uint64)]),
 }
 

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <cstdlib>
 #include <mutex>
+#include <algorithm>
 #include <new>
 #include <stdio.h>
 #include <string.h>
@@ -227,7 +228,9 @@ static int prepare_device(thrs_sorter* s, const DeviceState** out)
                     e = s->table->prepare[f][v]();
                     if (e == cudaSuccess) e = s->table->prepare_mid[f][v]();
                     if (e == cudaSuccess && s->table->prepare_scatter[f][v]) e = s->table->prepare_scatter[f][v]();
+                    if (e == cudaSuccess) e = s->table->prepare_seg[f][v]();
                 }
+            if (e == cudaSuccess) e = s->table->prepare_seg_histogram();
             for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare_small[v]();
             for (int v = 0; v < 4 && e == cudaSuccess; ++v) e = s->table->prepare_cluster[v](&ds.cluster_blocks[v]);
             if (e == cudaSuccess) e = s->table->prepare_histogram();
@@ -657,6 +660,208 @@ int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uin
     CUDA_TRY(s->table->scatter[fast][s->vslot](a, stream), "onesweep_kernel (scatter) launch");
     ++g_launches;
     return THRS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Segmented sort: nseg independent, contiguous segments of one array, every pass ONE launch over all
+// segments (kernels.cuh: SegTile, seg_histogram_kernel).  No counterpart in the reference (one sort per
+// call, hpp:845-852); the multi-GPU layer sorts the top-digit buckets a rank received with it (3 passes
+// on bits [0,24) instead of 4 on [0,32)), and it serves batches of independent sorts in general.
+// Scratch (u32 words): [segment table | tickets | hist[nseg][passes][256] | base[passes][nseg][256] |
+// per pass: status[vtiles][256], gsum[vtiles/16][256], gprefix[vtiles/16][256]].
+// ---------------------------------------------------------------------------------------------------
+namespace {
+struct SegScratch {
+    static constexpr uint64_t TABLE_WORDS = (SEG_TABLE_BYTES / 4);
+    static constexpr uint64_t TICKET_WORDS = 16;
+    static uint64_t vtiles_bound(uint64_t n_total, uint64_t nseg_batch, uint32_t tile)
+    {
+        return n_total / tile + (uint64_t)(GROUP_TILES + 1) * nseg_batch + GROUP_TILES;
+    }
+    static uint64_t words(uint64_t vtiles, uint64_t nseg_batch, uint64_t passes)
+    {
+        return TABLE_WORDS + TICKET_WORDS + 2 * nseg_batch * passes * RADIX + passes * (vtiles + 2 * (vtiles / GROUP_TILES + 1)) * RADIX;
+    }
+};
+uint32_t min_tile_of(const thrs_sorter* s)
+{
+    uint32_t t_min = 0xffffffffu;
+    for (int f = 0; f < 2; ++f) {
+        if (s->table->tile_items[f][0] < t_min) t_min = s->table->tile_items[f][0];
+        if (s->table->tile_items[f][s->vslot] < t_min) t_min = s->table->tile_items[f][s->vslot];
+    }
+    return t_min;
+}
+} // namespace
+
+uint64_t thrs_segments_scratch_bytes(const thrs_sorter* s, uint64_t n_total, uint32_t nseg)
+{
+    if (!s) return 0;
+    const uint64_t batch = nseg < (uint32_t)MAX_SEGMENTS ? (nseg ? nseg : 1) : MAX_SEGMENTS;
+    return align16(4ull * SegScratch::words(SegScratch::vtiles_bound(n_total, batch, min_tile_of(s)), batch, (uint64_t)s->kbytes));
+}
+
+int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_keys, void* alt_values, void* scratch,
+                          uint64_t scratch_bytes, const uint64_t* seg_begin, uint32_t nseg, int start_bits, int end_bits,
+                          void* stream_, int* result_in_alt)
+{
+    g_launches = 0;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (result_in_alt) *result_in_alt = 0;
+    if (!s || !seg_begin) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL argument");
+    if (start_bits < 0 || end_bits < start_bits) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_segments: need 0 <= startBits <= endBits");
+    if (((end_bits - start_bits) % 8) != 0) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_segments: (endBits - startBits) must be a multiple of 8");
+    const bool pairs = values != nullptr;
+    for (uint32_t i = 0; i < nseg; ++i) {
+        if (seg_begin[i + 1] < seg_begin[i]) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: seg_begin must ascend");
+        if (seg_begin[i + 1] - seg_begin[i] > (uint64_t)VALUE_MASK) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: a segment must stay below 2^30 items");
+    }
+    if (nseg == 0 || seg_begin[nseg] == seg_begin[0] || start_bits == end_bits) return THRS_OK;
+    if (seg_begin[nseg] > 0xffffffffull) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: offsets must stay below 2^32");
+    if (!keys || !alt_keys || !scratch || (pairs && !alt_values)) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL buffer");
+    if (((uintptr_t)keys % s->kbytes) != 0 || ((uintptr_t)alt_keys % s->kbytes) != 0 || ((uintptr_t)scratch % 16) != 0 ||
+        (pairs && (((uintptr_t)values % s->vbytes) != 0 || ((uintptr_t)alt_values % s->vbytes) != 0)))
+        return fail(THRS_ERR_ALIGNMENT, "thrs_sort_segments: misaligned buffer");
+    const int key_bits = s->kbytes * 8;
+    int passes = 0;
+    for (int b = start_bits; b < end_bits && b < key_bits; b += 8) ++passes;
+    if (passes == 0) return THRS_OK;
+    const DeviceState* ds = nullptr;
+    int prc = prepare_device(s, &ds);
+    if (prc) return prc;
+    const int fast = resolve_fast(s, *ds);
+    const int vslot = pairs ? s->vslot : 0;
+    const uint32_t tile = s->table->tile_items[fast][vslot];
+
+    std::vector<uint32_t> table(SegScratch::TABLE_WORDS);
+    for (uint32_t first_seg = 0; first_seg < nseg; first_seg += MAX_SEGMENTS) {
+        const uint32_t ns = nseg - first_seg < (uint32_t)MAX_SEGMENTS ? nseg - first_seg : (uint32_t)MAX_SEGMENTS;
+        // table of this batch: virtual tile ranges start at whole groups
+        std::fill(table.begin(), table.end(), 0u);
+        uint32_t* vt_first = table.data() + SEG_HEADER;
+        uint32_t* begin = vt_first + (MAX_SEGMENTS + 1);
+        uint32_t* count = begin + (MAX_SEGMENTS + 1);
+        uint64_t vt = 0;
+        for (uint32_t i = 0; i < ns; ++i) {
+            const uint64_t c = seg_begin[first_seg + i + 1] - seg_begin[first_seg + i];
+            vt_first[i] = (uint32_t)vt;
+            begin[i] = (uint32_t)seg_begin[first_seg + i];
+            count[i] = (uint32_t)c;
+            vt += div_up(div_up(c, tile), GROUP_TILES) * GROUP_TILES;
+        }
+        vt_first[ns] = (uint32_t)vt;
+        begin[ns] = (uint32_t)seg_begin[first_seg + ns];
+        table[0] = ns;
+        table[1] = (uint32_t)vt;
+        if (begin[ns] == begin[0]) continue; // only empty segments
+        const uint64_t vtiles = vt, vgroups = vt / GROUP_TILES + 1;
+        if (4ull * SegScratch::words(vtiles, ns, passes) > scratch_bytes)
+            return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: scratch too small (thrs_segments_scratch_bytes)");
+        uint32_t* w = static_cast<uint32_t*>(scratch);
+        uint32_t* d_table = w;
+        uint32_t* d_ticket = d_table + SegScratch::TABLE_WORDS;
+        uint32_t* d_hist = d_ticket + SegScratch::TICKET_WORDS;
+        uint32_t* d_base = d_hist + (uint64_t)ns * passes * RADIX;
+        uint32_t* d_pass = d_base + (uint64_t)ns * passes * RADIX;
+        const uint64_t pass_words = (vtiles + 2 * vgroups) * RADIX;
+        CUDA_TRY(cudaMemcpyAsync(d_table, table.data(), 4ull * SegScratch::TABLE_WORDS, cudaMemcpyHostToDevice, stream), "upload segment table");
+        // zero: tickets, histograms (bases are overwritten), status rows of the passes
+        CUDA_TRY(launch_zero(d_ticket, 4ull * (SegScratch::TICKET_WORDS + (uint64_t)ns * passes * RADIX), ds->sm_count, stream), "zero_kernel launch");
+        CUDA_TRY(launch_zero(d_pass, 4ull * passes * pass_words, ds->sm_count, stream), "zero_kernel launch");
+        g_launches += 2;
+        char* k_in = static_cast<char*>(keys);
+        char* k_out = static_cast<char*>(alt_keys);
+        char* v_in = static_cast<char*>(values);
+        char* v_out = static_cast<char*>(alt_values);
+        {
+            const uint64_t span = (uint64_t)begin[ns] - begin[0];
+            uint64_t grid = div_up(span, 1ull << 16);
+            if (grid > (uint64_t)ds->sm_count) grid = ds->sm_count;
+            if (grid == 0) grid = 1;
+            CUDA_TRY(s->table->seg_histogram(k_in, d_table, (uint32_t)start_bits, passes, d_hist, d_base, (int)ns, (int)grid, stream),
+                     "seg_histogram_kernel launch");
+            g_launches += 2;
+        }
+        for (int p = 0; p < passes; ++p) {
+            OnesweepArgs a;
+            a.keys_in = k_in;
+            a.keys_out = k_out;
+            a.vals_in = pairs ? v_in : nullptr;
+            a.vals_out = pairs ? v_out : nullptr;
+            a.n = begin[ns];
+            a.bit = (uint32_t)(start_bits + 8 * p);
+            a.status = d_pass + (uint64_t)p * pass_words;
+            a.gsum = a.status + vtiles * RADIX;
+            a.gprefix = a.gsum + vgroups * RADIX;
+            a.ticket = d_ticket + p;
+            a.sm_count = ds->sm_count;
+            a.base_in = d_base + (uint64_t)p * ns * RADIX;
+            a.base_out = nullptr;
+            a.pdl = false;
+            a.seg_table = d_table;
+            a.seg_vtiles = (uint32_t)vtiles;
+            CUDA_TRY(s->table->onesweep_seg[fast][vslot](a, stream), "onesweep_kernel (segmented) launch");
+            ++g_launches;
+            char* t = k_in; k_in = k_out; k_out = t;
+            t = v_in; v_in = v_out; v_out = t;
+        }
+        if ((passes & 1) && nseg > (uint32_t)MAX_SEGMENTS) {
+            // several batches share the buffers: bring this batch's range home so that all results lie in one place
+            const uint64_t off = begin[0], cnt = (uint64_t)begin[ns] - begin[0];
+            CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(keys) + off * s->kbytes, static_cast<char*>(alt_keys) + off * s->kbytes,
+                                     cnt * s->kbytes, cudaMemcpyDeviceToDevice, stream), "copy-back keys");
+            if (pairs)
+                CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(values) + off * s->vbytes, static_cast<char*>(alt_values) + off * s->vbytes,
+                                         cnt * s->vbytes, cudaMemcpyDeviceToDevice, stream), "copy-back values");
+        }
+    }
+    if (result_in_alt) *result_in_alt = ((passes & 1) && nseg <= (uint32_t)MAX_SEGMENTS) ? 1 : 0;
+    return THRS_OK;
+}
+
+static int sort_segments_in_place(thrs_sorter* s, void* keys, void* values, const uint64_t* seg_begin, uint32_t nseg, void* temp,
+                                  int start_bits, int end_bits, void* stream)
+{
+    if (!s || !seg_begin) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL argument");
+    if (nseg == 0) return THRS_OK;
+    if (!temp) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL buffer");
+    const uint64_t n_total = seg_begin[nseg];
+    const uint64_t sb = thrs_segments_scratch_bytes(s, n_total, nseg);
+    char* alt_k = static_cast<char*>(temp) + sb;
+    char* alt_v = alt_k + align16(n_total * s->kbytes);
+    int in_alt = 0;
+    int rc = thrs_sort_segments_ex(s, keys, values, alt_k, values ? alt_v : nullptr, temp, sb, seg_begin, nseg, start_bits, end_bits,
+                                   stream, &in_alt);
+    if (rc) return rc;
+    if (in_alt) {
+        const uint64_t off = seg_begin[0], cnt = seg_begin[nseg] - seg_begin[0];
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(keys) + off * s->kbytes, alt_k + off * s->kbytes, cnt * s->kbytes,
+                                 cudaMemcpyDeviceToDevice, st), "copy-back keys");
+        if (values)
+            CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(values) + off * s->vbytes, alt_v + off * s->vbytes, cnt * s->vbytes,
+                                     cudaMemcpyDeviceToDevice, st), "copy-back values");
+    }
+    return THRS_OK;
+}
+
+uint64_t thrs_segments_temp_bytes(const thrs_sorter* s, uint64_t n_total, uint32_t nseg, int with_values)
+{
+    if (!s) return 0;
+    return thrs_segments_scratch_bytes(s, n_total, nseg) + align16(n_total * s->kbytes) + (with_values ? align16(n_total * s->vbytes) : 0);
+}
+
+int thrs_sort_segments_keys(thrs_sorter* s, void* keys, const uint64_t* seg_begin, uint32_t nseg, void* temp, int start_bits,
+                            int end_bits, void* stream)
+{
+    return sort_segments_in_place(s, keys, nullptr, seg_begin, nseg, temp, start_bits, end_bits, stream);
+}
+
+int thrs_sort_segments_pairs(thrs_sorter* s, void* keys, void* values, const uint64_t* seg_begin, uint32_t nseg, void* temp,
+                             int start_bits, int end_bits, void* stream)
+{
+    if (!values) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments_pairs: NULL values");
+    return sort_segments_in_place(s, keys, values, seg_begin, nseg, temp, start_bits, end_bits, stream);
 }
 
 int thrs_ipc_export(void* device_ptr, void* handle64)

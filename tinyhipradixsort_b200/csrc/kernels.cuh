@@ -47,6 +47,24 @@ constexpr uint32_t GROUP_SUM_BITS = 26;
 constexpr uint32_t GROUP_SUM_MASK = (1u << GROUP_SUM_BITS) - 1u;
 constexpr int GROUP_LOOK = 4; // groups examined per round
 
+// ---- segmented launches (thrs_sort_segments_*, capi_seg.cu): one launch sorts up to MAX_SEGMENTS
+// independent, contiguous segments of one array.  Tickets run over VIRTUAL tiles: every segment owns a
+// range of virtual tiles that starts at a multiple of GROUP_TILES (so look-back groups never span two
+// segments) and is rounded up to whole groups; the padding tiles at the end of a range hold no items
+// and are skipped when drawn.  The first tile of a segment publishes an inclusive prefix right away,
+// exactly like tile 0 of an ordinary launch, so segments never wait on each other.
+constexpr int MAX_SEGMENTS = 256;
+constexpr int SEG_HEADER = 4; // [0] segments, [1] virtual tiles, [2..3] unused
+// device table (u32 words): header, vt_first[MAX_SEGMENTS + 1], begin[MAX_SEGMENTS + 1], count[MAX_SEGMENTS + 1]
+constexpr int SEG_TABLE_WORDS = SEG_HEADER + 3 * (MAX_SEGMENTS + 1);
+constexpr int SEG_TABLE_BYTES = (SEG_TABLE_WORDS * 4 + 15) & ~15;
+// s_misc words: [0,8) scan scratch, [12..15] tickets of ordinary launches; segmented launches keep the
+// description of a drawn tile in three slots of 8 words: two alternate in the pipelined loop (a slot is
+// read a full iteration after it was written), the third serves a block's first ticket and the
+// straight-line path
+constexpr int MISC_WORDS = 64;
+constexpr int TILE_SLOT0 = 16, TILE_SLOT_WORDS = 8, TILE_SLOT_LINE = TILE_SLOT0 + 2 * TILE_SLOT_WORDS;
+
 // Scratch ("pSumBuffer") layout in u32 words.  Fixed-size control block first, then the
 // look-back status rows of every pass: status[pass][tile][256].
 struct Scratch {
@@ -328,6 +346,129 @@ histogram_kernel(const KeyT* __restrict__ keys, uint32_t n, uint32_t start_bit, 
 }
 
 // ---------------------------------------------------------------------------------------
+// seg_histogram_kernel — histogram_kernel for a segmented sort: ONE read of the keys builds the 256-bin
+// histograms of every pass for every segment, hist[seg][pass][256] (zeroed by the caller).
+// The segments are contiguous, so the whole key range [begin[0], begin[nseg]) is cut into gridDim.x
+// equal slices; a block counts its slice segment by segment (a slice touches one or two segments when
+// there are fewer segments than blocks) and folds its lane-replicated table into the segment's
+// histogram whenever the segment changes.  seg_base_kernel then turns every histogram into absolute
+// exclusive bin bases, base[pass][seg][256] = begin[seg] + exclusive scan.
+// ---------------------------------------------------------------------------------------
+template <class KeyT, int KIND, bool DESC, int PASSES>
+__global__ void __launch_bounds__(HIST_THREADS, 1)
+seg_histogram_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__ seg_table, uint32_t start_bit,
+                     uint32_t* __restrict__ hist)
+{
+    using HS = HistShape<(int)sizeof(KeyT)>;
+    constexpr int REP = HS::REP;
+    constexpr int VEC = 16 / sizeof(KeyT);
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t* tab = reinterpret_cast<uint32_t*>(smem_raw); // [PASSES][256][REP]
+    const uint32_t nseg = seg_table[0];
+    const uint32_t* begin = seg_table + SEG_HEADER + (MAX_SEGMENTS + 1); // begin[nseg] = end of the last segment
+    const uint64_t first = begin[0], last = begin[nseg];
+    // whole multiples of 4096 items per slice
+    uint64_t per = (last - first + gridDim.x - 1) / gridDim.x;
+    per = (per + 4095ull) & ~4095ull;
+    const uint64_t lo = first + (uint64_t)blockIdx.x * per;
+    uint64_t hi = lo + per;
+    if (hi > last) hi = last;
+    if (lo >= hi) return;
+
+    auto zero_table = [&]() {
+        uint4* z = reinterpret_cast<uint4*>(tab);
+        for (int i = threadIdx.x; i < PASSES * RADIX * REP / 4; i += HIST_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    };
+    const uint32_t my = (uint32_t)__cvta_generic_to_shared(tab) + (threadIdx.x & (REP - 1)) * 4u;
+    auto count_key = [&](KeyT raw) {
+        if (sizeof(KeyT) == 4) {
+            const uint32_t kb = key_bits32<KIND, DESC>((uint32_t)raw) >> start_bit;
+#pragma unroll
+            for (int p = 0; p < PASSES; ++p) {
+                const uint32_t d = __byte_perm(kb, 0u, 0x4440u + p);
+                asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(my + (uint32_t)(p * RADIX * REP * 4) + d * (REP * 4u)) : "memory");
+            }
+        } else {
+            const uint64_t kb = key_bits64<KIND, DESC>((uint64_t)raw) >> start_bit;
+            const uint32_t l = (uint32_t)kb, h = (uint32_t)(kb >> 32);
+#pragma unroll
+            for (int p = 0; p < PASSES; ++p) {
+                const uint32_t d = __byte_perm(p < 4 ? l : h, 0u, 0x4440u + (p & 3));
+                asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(my + (uint32_t)(p * RADIX * REP * 4) + d * (REP * 4u)) : "memory");
+            }
+        }
+    };
+    auto count_vec = [&](uint4 a) {
+        if (sizeof(KeyT) == 4) {
+            count_key((KeyT)a.x); count_key((KeyT)a.y); count_key((KeyT)a.z); count_key((KeyT)a.w);
+        } else {
+            count_key((KeyT)(((uint64_t)a.y << 32) | a.x)); count_key((KeyT)(((uint64_t)a.w << 32) | a.z));
+        }
+    };
+
+    // last segment that begins at or before the slice (empty segments in between are skipped by the loop)
+    uint32_t seg = 0;
+    {
+        uint32_t a = 0, b = nseg; // begin[a] <= lo < begin[b]
+        while (b - a > 1u) {
+            const uint32_t m = (a + b) >> 1;
+            if ((uint64_t)begin[m] <= lo) a = m;
+            else b = m;
+        }
+        seg = a;
+    }
+    zero_table();
+    __syncthreads();
+    for (; seg < nseg && (uint64_t)begin[seg] < hi; ++seg) {
+        const uint64_t s0 = (uint64_t)begin[seg] > lo ? (uint64_t)begin[seg] : lo;
+        const uint64_t s1 = (uint64_t)begin[seg + 1] < hi ? (uint64_t)begin[seg + 1] : hi;
+        if (s1 <= s0) continue;
+        // head (until 16-byte alignment), vector body, tail of [s0, s1)
+        const KeyT* kp = keys + s0;
+        const uint32_t cnt = (uint32_t)(s1 - s0);
+        uint32_t head = (uint32_t)(((16 - ((uintptr_t)kp & 15)) & 15) / sizeof(KeyT));
+        if (head > cnt) head = cnt;
+        const uint32_t nvec = (cnt - head) / VEC;
+        const uint32_t tail_begin = head + nvec * VEC;
+        if (threadIdx.x < head) count_key(kp[threadIdx.x]);
+        if (tail_begin + threadIdx.x < cnt) count_key(kp[tail_begin + threadIdx.x]);
+        const uint4* vkeys = reinterpret_cast<const uint4*>(kp + head);
+        uint32_t v = threadIdx.x;
+        for (; (uint64_t)v + 3ull * HIST_THREADS < nvec; v += 4 * HIST_THREADS) {
+            uint4 a = __ldg(vkeys + v);
+            uint4 b = __ldg(vkeys + v + HIST_THREADS);
+            uint4 c = __ldg(vkeys + v + 2 * HIST_THREADS);
+            uint4 e = __ldg(vkeys + v + 3 * HIST_THREADS);
+            count_vec(a); count_vec(b); count_vec(c); count_vec(e);
+        }
+        for (; v < nvec; v += HIST_THREADS) count_vec(__ldg(vkeys + v));
+        __syncthreads();
+        uint32_t* g_hist = hist + (size_t)seg * PASSES * RADIX;
+        for (int r = threadIdx.x; r < PASSES * RADIX; r += HIST_THREADS) {
+            uint32_t c = 0;
+#pragma unroll
+            for (int i = 0; i < REP; ++i) c += tab[r * REP + ((i + threadIdx.x) & (REP - 1))];
+            if (c) atomicAdd(&g_hist[r], c);
+        }
+        __syncthreads();
+        zero_table();
+        __syncthreads();
+    }
+}
+
+// one block per (segment, pass): base[pass][seg][d] = begin[seg] + exclusive scan over d of hist[seg][pass][*]
+static __global__ void __launch_bounds__(RADIX)
+seg_base_kernel(const uint32_t* __restrict__ hist, const uint32_t* __restrict__ seg_table, int passes, uint32_t* __restrict__ base)
+{
+    __shared__ uint32_t s_scan[8];
+    const uint32_t nseg = seg_table[0];
+    const uint32_t seg = blockIdx.x / passes, p = blockIdx.x % passes;
+    const uint32_t c = hist[((size_t)seg * passes + p) * RADIX + threadIdx.x];
+    const uint32_t ex = block_exclusive_scan_256(c, s_scan, nullptr);
+    base[((size_t)p * nseg + seg) * RADIX + threadIdx.x] = seg_table[SEG_HEADER + (MAX_SEGMENTS + 1) + seg] + ex;
+}
+
+// ---------------------------------------------------------------------------------------
 // onesweep_kernel — one 8-bit pass over one part (< 2^30 items).
 // Replaces reorderKey/reorderKeyPair (kernel.cu:206-429) plus the per-(bin,block) half of
 // the reference's prefix scan.  Stable: equal digits keep their input order.
@@ -378,6 +519,50 @@ __device__ __forceinline__ uint32_t bin_or_digit(KeyT key, uint32_t bit, const B
     return b;
 }
 
+// What a block of a SEGMENTED launch knows about the tile behind a ticket (ordinary launches derive
+// everything from the ticket itself and never touch this).
+struct SegTile {
+    uint32_t seg = 0;    // segment
+    uint32_t offset = 0; // first item of the tile, relative to the launch's arrays
+    uint32_t valid = 0;  // items in the tile (TILE unless it is the last one of its segment)
+    uint32_t g0 = 0;     // first look-back group of the segment
+};
+// thread 0 of a segmented launch: draw tickets until one names a real tile (or runs past the end),
+// describe the tile in slot[1..4], leave the ticket in slot[0]
+template <int TILE>
+__device__ __forceinline__ void seg_tile_draw(uint32_t* __restrict__ ticket, uint32_t num_tiles, const uint32_t* s_seg,
+                                              uint32_t* slot)
+{
+    uint32_t t;
+    for (;;) {
+        t = atomicAdd(ticket, 1u);
+        if (t >= num_tiles) break;
+        const uint32_t* vt_first = s_seg + SEG_HEADER;
+        uint32_t lo = 0, hi = s_seg[0]; // vt_first[lo] <= t < vt_first[hi]; equal entries (empty segments) resolve to the last
+        while (hi - lo > 1u) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (vt_first[mid] <= t) lo = mid;
+            else hi = mid;
+        }
+        const uint32_t first_item = (t - vt_first[lo]) * (uint32_t)TILE;
+        const uint32_t cnt = s_seg[SEG_HEADER + 2 * (MAX_SEGMENTS + 1) + lo];
+        if (first_item < cnt) {
+            slot[1] = lo;
+            slot[2] = s_seg[SEG_HEADER + (MAX_SEGMENTS + 1) + lo] + first_item;
+            slot[3] = cnt - first_item < (uint32_t)TILE ? cnt - first_item : (uint32_t)TILE;
+            slot[4] = vt_first[lo] / GROUP_TILES;
+            break;
+        } // else: a padding tile (a segment's range of virtual tiles is rounded up to whole groups)
+    }
+    slot[0] = t;
+}
+__device__ __forceinline__ SegTile seg_tile_read(const uint32_t* slot)
+{
+    SegTile r;
+    r.seg = slot[1]; r.offset = slot[2]; r.valid = slot[3]; r.g0 = slot[4];
+    return r;
+}
+
 template <int VBYTES> struct ValueOf { using type = uint32_t; };
 template <> struct ValueOf<8> { using type = uint2; };
 template <> struct ValueOf<16> { using type = uint4; };
@@ -396,7 +581,7 @@ struct OnesweepSmem {
     static constexpr size_t OFF_VAL = OFF_TBL + TBL_BYTES; // 16-byte aligned (uint4 values)
     static constexpr size_t OFF_KEY = OFF_VAL + VAL_BYTES;
     static constexpr size_t OFF_BIN = OFF_KEY + KEY_BYTES;
-    static constexpr size_t OFF_PTR = OFF_BIN + RADIX * 4 + 64; // 8-byte aligned
+    static constexpr size_t OFF_PTR = OFF_BIN + RADIX * 4 + MISC_WORDS * 4; // 8-byte aligned
     static constexpr size_t OFF_RUN = OFF_PTR + 2 * RADIX * 8; // PEER: tile-local start and length of 8 bins
     static constexpr size_t BYTES = PEER ? OFF_RUN + 64 : OFF_PTR;
 };
@@ -419,8 +604,9 @@ __device__ __forceinline__ void load_tile_keys(KeyT (&key)[ITEMS], const KeyT* _
 
 // One tile.  `key` holds the tile's keys on entry and the NEXT tile's keys on return (they are
 // requested as soon as this tile's keys are staged, so their latency and the ticket's hide behind
-// the look-back and the read-out).  Returns the next tile's ticket.
-template <bool FULL, bool FAST, bool PEER, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
+// the look-back and the read-out).  Returns the next tile's ticket (SEG: its description in *seg_next).
+// SEG: `seg_cur` describes this tile (tile_base / tile_valid are taken from it by the caller).
+template <bool FULL, bool FAST, bool PEER, bool SEG, class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS>
 __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT* __restrict__ keys_in, uint32_t n,
                                               uint32_t num_tiles, uint32_t* __restrict__ ticket,
                                               KeyT* __restrict__ keys_out,
@@ -430,8 +616,11 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                                               uint32_t* __restrict__ gprefix, const uint32_t* __restrict__ base_in,
                                               uint32_t* __restrict__ base_out, uint32_t tile, bool last_tile,
                                               size_t tile_base, uint32_t tile_valid, unsigned char* smem_raw,
-                                              const BinThresholds& th)
+                                              const BinThresholds& th, const uint32_t* s_seg = nullptr,
+                                              const SegTile seg_cur = SegTile(), SegTile* seg_next = nullptr)
 {
+    const uint32_t g0 = SEG ? seg_cur.g0 : 0u;      // first look-back group and first tile of this tile's segment
+    const uint32_t t0 = SEG ? g0 * GROUP_TILES : 0u;
     using ValT = typename ValueOf<VBYTES>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST, PEER>;
     const unsigned long long* s_kptr = reinterpret_cast<const unsigned long long*>(smem_raw + SM::OFF_PTR);
@@ -447,7 +636,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
     ValT* s_vals = reinterpret_cast<ValT*>(smem_raw + SM::OFF_VAL);     // [TILE] tile-sorted
     KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw + SM::OFF_KEY);     // [TILE] tile-sorted
     uint32_t* s_off = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_BIN); // [256] global - local offset
-    uint32_t* s_misc = s_off + RADIX;                                   // [16]
+    uint32_t* s_misc = s_off + RADIX;                                   // [MISC_WORDS]
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -464,7 +653,9 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 
     const uint32_t my0 = warp * (32 * ITEMS) + lane;
     // ticket of the tile after this one: requested now, read after the scan's barriers
-    if (tid == 0) s_misc[14] = atomicAdd(ticket, 1u);
+    if (SEG) {
+        if (tid == 0) seg_tile_draw<THREADS * ITEMS>(ticket, num_tiles, s_seg, s_misc + TILE_SLOT_LINE);
+    } else if (tid == 0) s_misc[14] = atomicAdd(ticket, 1u);
 
     // ---- phase A: per-warp digit counts
 #pragma unroll
@@ -495,7 +686,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 #pragma unroll
             for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
             // early publication: successors can start summing while this tile still ranks
-            st_relaxed(my_status, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+            st_relaxed(my_status, (tile == t0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
             atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
         }
         bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
@@ -558,8 +749,11 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
     }
 
     // ---- this tile's keys are staged: request the next tile's into the same registers
-    const uint32_t next_tile = s_misc[14];
-    if (next_tile < num_tiles) {
+    const uint32_t next_tile = SEG ? s_misc[TILE_SLOT_LINE] : s_misc[14];
+    if (SEG) {
+        *seg_next = seg_tile_read(s_misc + TILE_SLOT_LINE);
+        if (next_tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, seg_next->offset, seg_next->valid);
+    } else if (next_tile < num_tiles) {
         const size_t nb = (size_t)next_tile * (size_t)(THREADS * ITEMS);
         const uint32_t nv = (n - nb) < (size_t)(THREADS * ITEMS) ? (uint32_t)(n - nb) : (uint32_t)(THREADS * ITEMS);
         load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, nb, nv);
@@ -572,7 +766,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
     // GROUP_LOOK complete groups (64 tiles) through their accumulator rows.
     if (tid < RADIX) {
         uint32_t excl = 0;
-        if (tile != 0) {
+        if (tile != t0) {
             const uint32_t g = tile / GROUP_TILES, r = tile % GROUP_TILES;
             const uint32_t* col = status + tid;
             const uint32_t* gs = gsum + tid;
@@ -583,7 +777,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                 v[i] = ((uint32_t)i < r) ? ld_relaxed(col + (size_t)(tile - 1 - i) * RADIX) : 0u;
 #pragma unroll
             for (int j = 0; j < GROUP_LOOK; ++j) {
-                const bool in = g >= (uint32_t)j + 1u; // group g-j has a predecessor group
+                const bool in = g >= g0 + (uint32_t)j + 1u; // group g-j has a predecessor group (in this segment)
                 gq[j] = in ? ld_relaxed(gp + (size_t)(g - j) * RADIX) : FLAG_PREFIX; // prefix through group g-j-1
                 ga[j] = in ? ld_relaxed(gs + (size_t)(g - j - 1) * RADIX) : 0u;      // accumulator of group g-j-1
             }
@@ -609,7 +803,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                     }
                 }
                 while (!have) { // beyond the prefetched rows, or a group still filling: poll (all its tiles run)
-                    const uint32_t q = gg == 0u ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
+                    const uint32_t q = gg == g0 ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
                     if ((q >> FLAG_SHIFT) == 2u) { pg += q & VALUE_MASK; have = true; break; }
                     const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
                     if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
@@ -619,7 +813,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
             }
             st_relaxed(my_status, FLAG_PREFIX | (excl + count));
         }
-        const uint32_t gbase = base_in[tid] + excl;
+        const uint32_t gbase = base_in[(SEG ? seg_cur.seg * RADIX : 0u) + tid] + excl;
         s_off[tid] = gbase - bin_start;
         if (base_out != nullptr && last_tile) base_out[tid] = gbase + count;
     }
@@ -677,13 +871,16 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 // aggregate (what successors mostly consume) is published as early as before.  Progress: a
 // block only ever spins on tickets lower than one it holds, and the block holding the lowest
 // unresolved ticket never spins.  The one partial tile (if any) is done by onesweep_tile<false>.
+// SEG: one launch over up to MAX_SEGMENTS independent segments (SegTile); seg_table is the device
+// table, base_in holds [segment][256] absolute bin bases of this pass.  A segment's partial last tile
+// is done by onesweep_tile<false> as soon as the pipeline has drained, then the loop goes on.
 // ---------------------------------------------------------------------------------------
 // PEER: the scatter pass of the multi-GPU layer.  Items are binned by destination (bin_or_digit), bin
 // b's items go, in input order, to peer_keys[b] / peer_vals[b] (device arrays of pointers, possibly
 // into other GPUs' memory over NVLink) from element base_in[b] on; keys_out / vals_out are unused.
 // A tile's run for one destination is ~TILE/ranks contiguous items, so the peer stores are long
 // full-line bursts (a 256-way digit split would send ~160-byte runs over the link).
-template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST, bool PEER>
+template <class KeyT, int KIND, bool DESC, int VBYTES, int THREADS, int ITEMS, int MINB, bool FAST, bool PEER, bool SEG = false>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 const typename ValueOf<VBYTES>::type* __restrict__ vals_in,
@@ -692,10 +889,11 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 uint32_t* __restrict__ gprefix, uint32_t* __restrict__ ticket,
                 const uint32_t* __restrict__ base_in, uint32_t* __restrict__ base_out,
                 const unsigned long long* __restrict__ peer_keys, const unsigned long long* __restrict__ peer_vals,
-                const BinThresholds th)
+                const BinThresholds th, const uint32_t* __restrict__ seg_table)
 {
     using ValT = typename ValueOf<VBYTES>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, THREADS, ITEMS, FAST, PEER>;
+    static_assert(!(PEER && SEG), "the scatter pass is never segmented");
     static_assert((uint64_t)GROUP_TILES * SM::TILE < (1ull << GROUP_SUM_BITS), "group accumulator overflow");
     static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit in the scan");
     constexpr int TILE = SM::TILE;
@@ -714,6 +912,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     unsigned long long* s_kptr = reinterpret_cast<unsigned long long*>(smem_raw + SM::OFF_PTR);
     unsigned long long* s_vptr = s_kptr + RADIX;
     uint32_t* s_run = reinterpret_cast<uint32_t*>(smem_raw + SM::OFF_RUN); // PEER only
+    uint32_t* s_seg = reinterpret_cast<uint32_t*>(smem_raw + SM::BYTES);   // SEG only: copy of seg_table
 
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -730,22 +929,32 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     auto base_word = [](uint32_t d) { return FAST ? d : 2u * d + (((d >> 4) & 1u) ^ 1u); };
     const uint32_t my0 = warp * (32 * ITEMS) + lane;
 
-    const uint32_t num_tiles = (n + TILE - 1) / TILE;
-    const uint32_t full_tiles = n / TILE;
+    if (SEG) { // the table is uploaded before the first launch of the sort and never written on the device
+        for (int i = tid; i < SEG_TABLE_WORDS; i += THREADS) s_seg[i] = seg_table[i];
+        __syncthreads();
+    }
+    const uint32_t num_tiles = SEG ? s_seg[1] : (n + TILE - 1) / TILE;
+    const uint32_t full_tiles = n / TILE; // ordinary launches only
 
     // First ticket before the wait: safe because this block can only have been scheduled after every
     // histogram block passed ITS griddepcontrol.wait on zero_kernel (histogram_kernel triggers its
     // dependents after that wait), so the ticket word is zero and nobody clears it again.
-    if (tid == 0) s_misc[15] = atomicAdd(ticket, 1u);
+    if (SEG) {
+        if (tid == 0) seg_tile_draw<TILE>(ticket, num_tiles, s_seg, s_misc + TILE_SLOT_LINE);
+    } else if (tid == 0) s_misc[15] = atomicAdd(ticket, 1u);
     {
         uint4* z = reinterpret_cast<uint4*>(smem_raw + SM::OFF_TBL);
         for (int i = tid; i < (int)(SM::TBL_BYTES / 16); i += THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
     if (!PEER) pdl_wait(); // keys, values and bin bases of the previous launch are complete and visible from here
     __syncthreads();
-    uint32_t tile = s_misc[15];
+    uint32_t tile = SEG ? s_misc[TILE_SLOT_LINE] : s_misc[15];
+    SegTile sg, p_sg; // SEG only: the current tile and the one whose read-out is pending
+    if (SEG) sg = seg_tile_read(s_misc + TILE_SLOT_LINE);
     KeyT key[ITEMS];
-    if (tile < num_tiles) {
+    if (SEG) {
+        if (tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, sg.offset, sg.valid);
+    } else if (tile < num_tiles) {
         const size_t tb = (size_t)tile * TILE;
         load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, tb, (n - tb) < (size_t)TILE ? (uint32_t)(n - tb) : (uint32_t)TILE);
     }
@@ -756,10 +965,29 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     uint32_t iter = 0;
     PHASE_BEGIN();
     while (true) {
-        const bool cur = tile < full_tiles; // block-uniform
-        if (!cur && !have_prev) break;
+        const bool cur = SEG ? (tile < num_tiles && sg.valid == (uint32_t)TILE) : (tile < full_tiles); // block-uniform
+        if (!cur && !have_prev) {
+            if (!SEG || tile >= num_tiles) break;
+            // SEG: the partial last tile of a segment and nothing in flight: straight-line path; like an
+            // iteration of this loop it leaves the next tile's keys in `key`
+            SegTile nx;
+            tile = onesweep_tile<false, FAST, PEER, SEG, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
+                key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
+                base_out, tile, false, (size_t)sg.offset, sg.valid, smem_raw, th, s_seg, sg, &nx);
+            sg = nx;
+            // nothing of the drained pipeline is needed any more: say so, or ptxas keeps the look-back registers
+            // alive (and spills them in the hot loop) across the straight-line tile
+#pragma unroll
+            for (int i = 0; i < GROUP_TILES - 1; ++i) lb_v[i] = 0u;
+#pragma unroll
+            for (int j = 0; j < GROUP_LOOK; ++j) { lb_ga[j] = 0u; lb_gq[j] = 0u; }
+            p_tile = 0; p_count = 0; p_bin_start = 0; p_sg = SegTile();
+            continue;
+        }
         PHASE_MARK(8); // issue of the look-back loads and the key prefetch (waits for phase C's stores to drain)
-        const size_t tile_base = (size_t)tile * TILE;
+        const size_t tile_base = SEG ? (size_t)sg.offset : (size_t)tile * TILE;
+        const uint32_t g0 = SEG ? sg.g0 : 0u;          // first look-back group / first tile of this tile's segment
+        const uint32_t t0 = SEG ? g0 * GROUP_TILES : 0u;
         uint32_t count = 0;
         bool warp_one_digit = false;
         uint32_t warp_digit = 0;
@@ -768,7 +996,9 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         bool warp_rank_wide = false;
         if (cur) {
             // ticket of the tile after this one (slot alternates: it is read a full iteration later)
-            if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
+            if (SEG) {
+                if (tid == 0) seg_tile_draw<TILE>(ticket, num_tiles, s_seg, s_misc + TILE_SLOT0 + TILE_SLOT_WORDS * (iter & 1u));
+            } else if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
 #ifdef THRS_PHASE_TIMING
             if (tid == 0 && s_misc[12 + (iter & 1u)] < 32768u) g_trace[0][s_misc[12 + (iter & 1u)]] = trace_now();
 #endif
@@ -842,7 +1072,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (cur && tid < RADIX) {
 #pragma unroll
             for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
-            st_relaxed(status + (size_t)tile * RADIX + tid, (tile == 0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+            st_relaxed(status + (size_t)tile * RADIX + tid, (tile == t0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
             atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
             TRACE(1, tile);
         }
@@ -863,7 +1093,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (have_prev && tid < RADIX) {
             uint32_t excl = 0;
             TRACE(4, p_tile);
-            if (p_tile != 0) {
+            if (p_tile != (SEG ? p_sg.g0 * GROUP_TILES : 0u)) {
                 const uint32_t g = p_tile / GROUP_TILES, r = p_tile % GROUP_TILES;
                 const uint32_t* col = status + tid;
                 const uint32_t* gs = gsum + tid;
@@ -896,7 +1126,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                     }
                     while (!have) { // beyond the prefetched rows, or a group still filling: poll
                         LB_COUNT(4);
-                        const uint32_t q = gg == 0u ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
+                        const uint32_t q = gg == (SEG ? p_sg.g0 : 0u) ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
                         if ((q >> FLAG_SHIFT) == 2u) { pg += q & VALUE_MASK; have = true; break; }
                         const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
                         if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
@@ -907,7 +1137,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 st_relaxed(status + (size_t)p_tile * RADIX + tid, FLAG_PREFIX | (excl + p_count));
             }
             TRACE(5, p_tile);
-            const uint32_t gbase = base_in[tid] + excl;
+            const uint32_t gbase = base_in[(SEG ? p_sg.seg * RADIX : 0u) + tid] + excl;
             s_off[tid] = gbase - p_bin_start;
             if (base_out != nullptr && p_tile == num_tiles - 1) base_out[tid] = gbase + p_count;
             if (PEER && tid < 8) {
@@ -995,10 +1225,16 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         PHASE_MARK(14);
         __syncthreads();
         PHASE_MARK(15);
-        if (!cur) break;
+        if (!cur) {
+            if (!SEG) break;
+            have_prev = false; // SEG: the pipeline is drained, the segment's partial tile (if any) is next
+            continue;
+        }
 
         // ---- phase C(tile): rank and stage at the tile-sorted position
-        const uint32_t next_tile = s_misc[12 + (iter & 1u)];
+        const uint32_t next_tile = SEG ? s_misc[TILE_SLOT0 + TILE_SLOT_WORDS * (iter & 1u)] : s_misc[12 + (iter & 1u)];
+        SegTile next_sg;
+        if (SEG) next_sg = seg_tile_read(s_misc + TILE_SLOT0 + TILE_SLOT_WORDS * (iter & 1u));
         const uint32_t lane_bit = 1u << lane;
         const uint32_t lane_lt = lane_bit - 1u;
         if (warp_one_digit) {
@@ -1071,31 +1307,34 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
 
         // ---- look-back loads of this tile (consumed next iteration), then the next tile's keys
         TRACE(2, tile); TRACE(3, tile);
-        if (tid < RADIX && tile != 0) {
+        if (tid < RADIX && tile != t0) {
             const uint32_t g = tile / GROUP_TILES, r = tile % GROUP_TILES;
 #pragma unroll
             for (int i = 0; i < GROUP_TILES - 1; ++i)
                 lb_v[i] = ((uint32_t)i < r) ? ld_relaxed(status + tid + (size_t)(tile - 1 - i) * RADIX) : 0u;
 #pragma unroll
             for (int j = 0; j < GROUP_LOOK; ++j) {
-                const bool in = g >= (uint32_t)j + 1u; // group g-j has a predecessor group
+                const bool in = g >= g0 + (uint32_t)j + 1u; // group g-j has a predecessor group (in this segment)
                 lb_gq[j] = in ? ld_relaxed(gprefix + tid + (size_t)(g - j) * RADIX) : FLAG_PREFIX;
                 lb_ga[j] = in ? ld_relaxed(gsum + tid + (size_t)(g - j - 1) * RADIX) : 0u;
             }
         }
-        if (next_tile < num_tiles) {
+        if (SEG) {
+            if (next_tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, next_sg.offset, next_sg.valid);
+        } else if (next_tile < num_tiles) {
             const size_t nb = (size_t)next_tile * TILE;
             load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, nb, (n - nb) < (size_t)TILE ? (uint32_t)(n - nb) : (uint32_t)TILE);
         }
         p_tile = tile; p_count = count; p_bin_start = bin_start; have_prev = true;
+        if (SEG) { p_sg = sg; sg = next_sg; }
         tile = next_tile;
         ++iter;
     }
 
     // ---- the partial last tile, if this block drew its ticket (straight-line path)
-    if (tile == full_tiles && full_tiles < num_tiles) {
+    if (!SEG && tile == full_tiles && full_tiles < num_tiles) {
         const size_t tile_base = (size_t)tile * TILE;
-        onesweep_tile<false, FAST, PEER, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
+        onesweep_tile<false, FAST, PEER, false, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
             key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
             base_out, tile, true, tile_base, (uint32_t)(n - tile_base), smem_raw, th);
     }

@@ -33,7 +33,7 @@ template <bool FAST> struct Tuning<4, 0, FAST> {
 // Match-mask cells are 8 bytes (16 KiB table instead of 8): those shapes stage one or two items less per
 // thread so that two blocks still fit (static_assert in launch_onesweep; the scatter variant adds 4 KiB).
 template <bool FAST> struct Tuning<4, 8, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 32 : 30, MINB = 2; };
-template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 20 : 19, MINB = 2; };
+template <bool FAST> struct Tuning<4, 16, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 20 : 18, MINB = 2; };
 template <bool FAST> struct Tuning<8, 0, FAST> { static constexpr int THREADS = 256, ITEMS = 40, MINB = 2; };
 template <bool FAST> struct Tuning<8, 4, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 32 : 30, MINB = 2; };
 template <bool FAST> struct Tuning<8, 8, FAST> { static constexpr int THREADS = 256, ITEMS = FAST ? 24 : 22, MINB = 2; };
@@ -77,6 +77,9 @@ struct OnesweepArgs {
     // programmatic dependent launch: this launch directly follows, on the same stream, the kernel
     // that produced its inputs (the histogram or the previous pass)
     bool pdl = false;
+    // segmented launch only: device table (SEG_TABLE_WORDS words) and its number of virtual tiles
+    const uint32_t* seg_table = nullptr;
+    uint32_t seg_vtiles = 0;
 };
 
 struct KernelTable {
@@ -96,6 +99,12 @@ struct KernelTable {
     // scatter pass (per-digit destination pointers); 4- and 8-byte values only, else nullptr
     cudaError_t (*scatter[2][4])(const OnesweepArgs& a, cudaStream_t stream);
     cudaError_t (*prepare_scatter[2][4])();
+    // segmented pass (several independent segments in one launch); same index meaning as onesweep
+    cudaError_t (*onesweep_seg[2][4])(const OnesweepArgs& a, cudaStream_t stream);
+    cudaError_t (*prepare_seg[2][4])();
+    cudaError_t (*seg_histogram)(const void* keys, const uint32_t* seg_table, uint32_t start_bit, int passes, uint32_t* hist,
+                                 uint32_t* base, int nseg, int grid, cudaStream_t stream);
+    cudaError_t (*prepare_seg_histogram)();
     // one-block sort for n <= SMALL_SORT_MAX (small_sort.cuh)
     cudaError_t (*small[4])(void* keys, void* vals, uint32_t n, uint32_t start_bit, int passes, cudaStream_t stream);
     cudaError_t (*prepare_small[4])();
@@ -179,41 +188,99 @@ cudaError_t prepare_histogram()
     return e;
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false>
+// segmented histogram + bases: hist[nseg][passes][256] must be zero on entry
+template <class KeyT, int KIND, bool DESC, int PASSES>
+cudaError_t launch_seg_histogram_p(const void* keys, const uint32_t* seg_table, uint32_t start_bit, uint32_t* hist, int grid,
+                                   cudaStream_t stream)
+{
+    seg_histogram_kernel<KeyT, KIND, DESC, PASSES><<<grid, HIST_THREADS, HistShape<(int)sizeof(KeyT)>::BYTES, stream>>>(
+        static_cast<const KeyT*>(keys), seg_table, start_bit, hist);
+    return cudaGetLastError();
+}
+template <class KeyT, int KIND, bool DESC>
+cudaError_t launch_seg_histogram(const void* keys, const uint32_t* seg_table, uint32_t start_bit, int passes, uint32_t* hist,
+                                 uint32_t* base, int nseg, int grid, cudaStream_t stream)
+{
+    cudaError_t e = cudaErrorInvalidValue;
+    switch (passes) {
+    case 1: e = launch_seg_histogram_p<KeyT, KIND, DESC, 1>(keys, seg_table, start_bit, hist, grid, stream); break;
+    case 2: e = launch_seg_histogram_p<KeyT, KIND, DESC, 2>(keys, seg_table, start_bit, hist, grid, stream); break;
+    case 3: e = launch_seg_histogram_p<KeyT, KIND, DESC, 3>(keys, seg_table, start_bit, hist, grid, stream); break;
+    case 4: e = launch_seg_histogram_p<KeyT, KIND, DESC, 4>(keys, seg_table, start_bit, hist, grid, stream); break;
+    default: break;
+    }
+    if (sizeof(KeyT) == 8) {
+        switch (passes) {
+        case 5: e = launch_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 5 : 1>(keys, seg_table, start_bit, hist, grid, stream); break;
+        case 6: e = launch_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 6 : 1>(keys, seg_table, start_bit, hist, grid, stream); break;
+        case 7: e = launch_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 7 : 1>(keys, seg_table, start_bit, hist, grid, stream); break;
+        case 8: e = launch_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 8 : 1>(keys, seg_table, start_bit, hist, grid, stream); break;
+        default: break;
+        }
+    }
+    if (e != cudaSuccess) return e;
+    seg_base_kernel<<<nseg * passes, RADIX, 0, stream>>>(hist, seg_table, passes, base);
+    return cudaGetLastError();
+}
+template <class KeyT, int KIND, bool DESC, int PASSES>
+cudaError_t prepare_seg_histogram_p()
+{
+    return cudaFuncSetAttribute(seg_histogram_kernel<KeyT, KIND, DESC, PASSES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)HistShape<(int)sizeof(KeyT)>::BYTES);
+}
+template <class KeyT, int KIND, bool DESC>
+cudaError_t prepare_seg_histogram()
+{
+    cudaError_t e = prepare_seg_histogram_p<KeyT, KIND, DESC, 1>();
+    if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, 2>();
+    if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, 3>();
+    if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, 4>();
+    if (sizeof(KeyT) == 8) {
+        if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 5 : 1>();
+        if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 6 : 1>();
+        if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 7 : 1>();
+        if (e == cudaSuccess) e = prepare_seg_histogram_p<KeyT, KIND, DESC, sizeof(KeyT) == 8 ? 8 : 1>();
+    }
+    return e;
+}
+
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false, bool SEG = false>
 cudaError_t launch_onesweep(const OnesweepArgs& a, cudaStream_t stream)
 {
     using T = typename ShapeOf<(int)sizeof(KeyT), VBYTES, FAST, MID>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
     using ValT = typename ValueOf<VBYTES>::type;
+    constexpr size_t SMEM = SM::BYTES + (SEG ? SEG_TABLE_BYTES : 0);
     // MINB blocks must really fit one SM (228 KiB shared memory, 1 KiB reserved per block): the grid below assumes it
-    static_assert((size_t)T::MINB * (SM::BYTES + 1024) <= 233472, "tile shape does not fit MINB blocks per SM");
-    const uint32_t tiles = (a.n + SM::TILE - 1) / SM::TILE;
+    static_assert((size_t)T::MINB * (SMEM + 1024) <= 233472, "tile shape does not fit MINB blocks per SM");
+    const uint32_t tiles = SEG ? a.seg_vtiles : (a.n + SM::TILE - 1) / SM::TILE;
     // persistent blocks, T::MINB per SM; correctness does not depend on all of them being resident
     const uint32_t cap = (uint32_t)a.sm_count * T::MINB;
     const uint32_t grid = tiles < cap ? tiles : cap;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(T::THREADS);
-    cfg.dynamicSmemBytes = SM::BYTES;
+    cfg.dynamicSmemBytes = SMEM;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = a.pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER>,
+    return cudaLaunchKernelEx(&cfg, onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER, SEG>,
                               static_cast<const KeyT*>(a.keys_in), static_cast<KeyT*>(a.keys_out),
                               static_cast<const ValT*>(a.vals_in), static_cast<ValT*>(a.vals_out), a.n, a.bit, a.bit, a.status,
-                              a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out, a.peer_keys, a.peer_vals, a.thresholds);
+                              a.gsum, a.gprefix, a.ticket, a.base_in, a.base_out, a.peer_keys, a.peer_vals, a.thresholds,
+                              a.seg_table);
 }
 
-template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false>
+template <class KeyT, int KIND, bool DESC, int VBYTES, bool FAST, bool PEER = false, bool MID = false, bool SEG = false>
 cudaError_t prepare_onesweep()
 {
     using T = typename ShapeOf<(int)sizeof(KeyT), VBYTES, FAST, MID>::type;
     using SM = OnesweepSmem<KeyT, VBYTES, T::THREADS, T::ITEMS, FAST, PEER>;
-    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES);
+    return cudaFuncSetAttribute(onesweep_kernel<KeyT, KIND, DESC, VBYTES, T::THREADS, T::ITEMS, T::MINB, FAST, PEER, SEG>,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SM::BYTES + (SEG ? SEG_TABLE_BYTES : 0)));
 }
 
 template <int KB, int VB> constexpr uint32_t mid_tile_of() { return (uint32_t)(MidTuning<KB, VB>::THREADS * MidTuning<KB, VB>::ITEMS); }
@@ -249,6 +316,16 @@ const KernelTable* make_table()
          {nullptr, &launch_onesweep<KeyT, KIND, DESC, 4, true, true>, &launch_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}},
         {{nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, false, true>, nullptr},
          {nullptr, &prepare_onesweep<KeyT, KIND, DESC, 4, true, true>, &prepare_onesweep<KeyT, KIND, DESC, 8, true, true>, nullptr}},
+        {{&launch_onesweep<KeyT, KIND, DESC, 0, false, false, false, true>, &launch_onesweep<KeyT, KIND, DESC, 4, false, false, false, true>,
+          &launch_onesweep<KeyT, KIND, DESC, 8, false, false, false, true>, &launch_onesweep<KeyT, KIND, DESC, 16, false, false, false, true>},
+         {&launch_onesweep<KeyT, KIND, DESC, 0, true, false, false, true>, &launch_onesweep<KeyT, KIND, DESC, 4, true, false, false, true>,
+          &launch_onesweep<KeyT, KIND, DESC, 8, true, false, false, true>, &launch_onesweep<KeyT, KIND, DESC, 16, true, false, false, true>}},
+        {{&prepare_onesweep<KeyT, KIND, DESC, 0, false, false, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 4, false, false, false, true>,
+          &prepare_onesweep<KeyT, KIND, DESC, 8, false, false, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 16, false, false, false, true>},
+         {&prepare_onesweep<KeyT, KIND, DESC, 0, true, false, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 4, true, false, false, true>,
+          &prepare_onesweep<KeyT, KIND, DESC, 8, true, false, false, true>, &prepare_onesweep<KeyT, KIND, DESC, 16, true, false, false, true>}},
+        &launch_seg_histogram<KeyT, KIND, DESC>,
+        &prepare_seg_histogram<KeyT, KIND, DESC>,
         {&launch_small_sort<KeyT, KIND, DESC, 0>, &launch_small_sort<KeyT, KIND, DESC, 4>,
          &launch_small_sort<KeyT, KIND, DESC, 8>, &launch_small_sort<KeyT, KIND, DESC, 16>},
         {&prepare_small_sort<KeyT, KIND, DESC, 0>, &prepare_small_sort<KeyT, KIND, DESC, 4>,

@@ -232,6 +232,22 @@ class RadixSort:
         _check(self._lib.thrs_digit_histogram(self._h, _ptr(keyBuffer), int(numberOfInputs), int(startBit),
                                               _ptr(countsOut), _ptr(temporaryBuffer), _stream(stream)))
 
+    # -- not in the reference: many independent sorts in one set of launches (thrs_sort_segments_*)
+    def getSegmentsTemporaryBufferBytes(self, totalInputs, numberOfSegments, withValues=True):
+        return int(self._lib.thrs_segments_temp_bytes(self._h, int(totalInputs), int(numberOfSegments), int(bool(withValues))))
+
+    def sortSegments(self, keyBuffer, valueBuffer, segmentBegin, temporaryBuffer, startBits, endBits, stream=None):
+        """Sort every segment [segmentBegin[i], segmentBegin[i+1]) of the arrays on its own (stable,
+        in place).  segmentBegin: ascending host offsets, len = segments + 1; valueBuffer None = keys only."""
+        seg = (ctypes.c_uint64 * len(segmentBegin))(*[int(x) for x in segmentBegin])
+        nseg = len(segmentBegin) - 1
+        if valueBuffer is None:
+            _check(self._lib.thrs_sort_segments_keys(self._h, _ptr(keyBuffer), seg, nseg, _ptr(temporaryBuffer),
+                                                     int(startBits), int(endBits), _stream(stream)))
+        else:
+            _check(self._lib.thrs_sort_segments_pairs(self._h, _ptr(keyBuffer), _ptr(valueBuffer), seg, nseg,
+                                                      _ptr(temporaryBuffer), int(startBits), int(endBits), _stream(stream)))
+
     # -- not in the reference: what unittest.cpp:399-414 does around a sort, in one C-ABI call
     def sortHost(self, host_keys, host_values, startBits, endBits):
         """Sort numpy arrays / CPU tensors in place (H2D, sort, D2H inside the call)."""
