@@ -176,6 +176,19 @@ THRS_API int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, voi
                                    uint64_t scratch_bytes, const uint64_t* seg_begin, uint32_t nseg, int start_bits,
                                    int end_bits, void* stream, int* result_in_alt);
 
+/* One stable 8-bit pass, OUT OF PLACE (the reference's reorderKeyPair, kernel.cu:206-429, is out of
+ * place too: hpp:897-922 ping-pongs): (keys, values) -> (out_keys, out_values) ordered by the digit
+ * (getKeyBits(key) >> bit) & 0xFF in sort order, ties in input order; the inputs are only read.  Also
+ * leaves the 256-bin digit histogram in counts_out (device, 256 uint32; may be NULL) and, if
+ * counts_ready_event (a cudaEvent_t) is given, records it on `stream` as soon as counts_out is
+ * written — before the pass itself runs — so that a second stream can ship the histogram meanwhile.
+ * temp: thrs_temp_bytes(n).pSumBuffer bytes.  n may exceed 2^30 (cut in parts like a sort).  This is
+ * the MSD step of the multi-GPU sort: after it, bucket d is the contiguous range
+ * [sum(counts[0..d)), sum(counts[0..d])) of the outputs. */
+THRS_API int thrs_partition_pairs(thrs_sorter* s, const void* keys, const void* values, uint32_t n, void* temp,
+                                  void* out_keys, void* out_values, int bit, uint32_t* counts_out,
+                                  void* counts_ready_event, void* stream);
+
 /* Multi-GPU layer (no counterpart in the reference, single device: unittest.cpp:22,51).
  * thrs_scatter_pairs: ONE stable pass over the 8-bit digit at start_bit (in sort order, i.e. of
  * getKeyBits ^ order mask) that splits the input into nbins <= 8 destination bins: bin b takes the
@@ -195,15 +208,57 @@ THRS_API int thrs_ipc_export(void* device_ptr, void* handle64);
 THRS_API int thrs_ipc_open(const void* handle64, void** out_device_ptr);
 THRS_API int thrs_ipc_close(void* device_ptr);
 
+/* Exchange layer of the multi-GPU sort: one context per rank (= per GPU), for hosts that run one
+ * process per GPU (windows opened with thrs_ipc_*) and for thrs_mg_* below (plain peer access).
+ * The sort of the concatenated slices is:
+ *   thrs_xchg_begin   top-digit histogram of the slice + ONE stable out-of-place pass on the top digit
+ *                     (thrs_partition_pairs — this is the sort's last radix pass, not an extra one); a
+ *                     side stream pushes the 256 counts into every rank's window with the copy engines
+ *                     and reads the gathered table back (no NCCL, no SM).  Returns without waiting.
+ *   thrs_xchg_finish  waits (host) for the gathered table, picks splitters on digit boundaries (equal
+ *                     keys never straddle ranks), and enqueues: copy-engine copies of every (digit,
+ *                     source) chunk straight into the owner's window, DIGIT-MAJOR / SOURCE-MINOR, group
+ *                     by group, a 4-byte flag after each group; on `stream`, per group, a
+ *                     cuStreamWaitValue32 on the group's flags and a segmented sort
+ *                     (thrs_sort_segments_ex, one segment per digit) on bits [0, key bits - 8) while
+ *                     later groups are still in flight.  Returns device pointers (owned by the
+ *                     context, valid until its next begin) to this rank's sorted share.
+ * Concatenating the shares of rank 0..world-1 is exactly std::stable_sort of the concatenated slices
+ * (ties in (rank, position) order).  Every rank must call begin / finish the same number of times
+ * (flags are epoch numbers).  max_local_items bounds a slice, capacity_items what a rank can receive
+ * (whole top-digit buckets: skew can exceed n/world); if a share would not fit, EVERY rank's finish
+ * fails alike with the largest share in *needed_capacity and nothing has been copied.  4- and 8-byte
+ * values; slices and shares below 2^32 items.  groups: pipeline depth per rank (1..16, 4 is a good
+ * default).  thrs_xchg_plan is the host-only planning step (owner, share and group of every top
+ * digit from the [world][256] count table), exported for tests and for hosts that want the layout. */
+typedef struct thrs_xchg thrs_xchg;
+THRS_API int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_local_items, uint64_t capacity_items,
+                              int groups, thrs_xchg** out);
+THRS_API void thrs_xchg_destroy(thrs_xchg* x);
+/* The memory other ranks write into (export it with thrs_ipc_export) ... */
+THRS_API int thrs_xchg_window(thrs_xchg* x, void** base, uint64_t* bytes);
+/* ... and every rank's window as a device address valid in THIS process (thrs_ipc_open), own one included. */
+THRS_API int thrs_xchg_set_peers(thrs_xchg* x, void* const* window_bases);
+THRS_API int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t n, void* stream);
+THRS_API int thrs_xchg_finish(thrs_xchg* x, void* stream, void** out_keys, void** out_values, uint64_t* out_count,
+                              uint64_t* needed_capacity);
+/* Of the last begin/finish pair: items received, bytes sent to OTHER ranks, kernels launched, bucket copies enqueued. */
+THRS_API int thrs_xchg_stats(thrs_xchg* x, uint64_t* received_items, uint64_t* sent_remote_bytes, uint32_t* kernel_launches,
+                             uint32_t* bucket_copies);
+THRS_API int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner_of_digit, uint64_t* recv_totals,
+                            int32_t* group_of_digit);
+THRS_API const char* thrs_xchg_last_error(void);
+
 /* Single-process multi-GPU sort (SURVEY.md 8(b) plan: thrs_mg_create / thrs_mg_sort_pairs /
- * thrs_mg_destroy): one host thread drives up to 8 peer-capable devices of one box.  keys[g] /
- * values[g] are device pointers on device_ids[g] holding counts[g] items (< 2^30 each, 64-bit
- * counts at this layer; the inputs are only read).  out_keys[g] / out_values[g] are buffers on the
- * same devices with room for out_capacity[g] items.  On return out_counts[g] items lie in each
- * output, and the concatenation over g = 0..ndev-1 is exactly std::stable_sort of the concatenated
- * inputs (ties in (device, position) order).  The split is by whole top-digit buckets, so an
- * output can receive more than total/ndev items: if a capacity is too small the call fails with
- * THRS_ERR_INVALID_ARGUMENT and the needed sizes in out_counts.  Blocking; 4- and 8-byte values. */
+ * thrs_mg_destroy): one host thread drives up to 8 peer-capable devices of one box through the
+ * exchange layer above (device ids may repeat: several ranks on one GPU).  keys[g] / values[g] are
+ * device pointers on device_ids[g] holding counts[g] items (< 2^32 each, 64-bit counts at this
+ * layer; the inputs are only read).  out_keys[g] / out_values[g] are buffers on the same devices
+ * with room for out_capacity[g] items.  On return out_counts[g] items lie in each output, and the
+ * concatenation over g = 0..ndev-1 is exactly std::stable_sort of the concatenated inputs (ties in
+ * (device, position) order).  The split is by whole top-digit buckets, so an output can receive more
+ * than total/ndev items: if a capacity is too small the call fails with THRS_ERR_INVALID_ARGUMENT and
+ * the needed sizes in out_counts.  Blocking; 4- and 8-byte values. */
 typedef struct thrs_mg thrs_mg;
 THRS_API int thrs_mg_create(int ndev, const int* device_ids, const thrs_config* cfg, thrs_mg** out);
 THRS_API void thrs_mg_destroy(thrs_mg* m);

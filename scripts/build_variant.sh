@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")/../tinyhipradixsort_b200/csrc"
 out=../../build/variants/$1; mkdir -p $out/obj
-for f in capi capi_mg inst_u32 inst_u64 inst_f32 inst_f64; do
+for f in capi capi_mg capi_xchg inst_u32 inst_u64 inst_f32 inst_f64; do
   /usr/local/cuda/bin/nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-fvisibility=hidden $2 -c $f.cu -o $out/obj/$f.o &
 done
 wait

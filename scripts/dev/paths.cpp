@@ -1,6 +1,7 @@
 // paths.cpp — dev/sanitizer driver: ONE sort through every kernel path of libthrs_b200.so (one-block,
 // cluster of 2/4/8 blocks, quarter-tile "mid" shape, full-size tiles keys-only and pairs, both rankings,
-// the PEER scatter pass with local destinations), each checked on the host.  Meant to be run under
+// the PEER scatter pass with local destinations, the segmented sort, the exchange layer with two ranks on
+// one device), each checked on the host.  Meant to be run under
 //   compute-sanitizer --tool memcheck|racecheck|synccheck scripts/dev/paths
 // (scripts/sanitize.sh); sizes are kept small because racecheck slows kernels down ~100x.
 #include <cuda_runtime.h>
@@ -90,6 +91,76 @@ static int run_scatter(thrs_sorter* s, uint32_t n)
     return bad;
 }
 
+// segmented sort: uneven segments incl. empty and partial-tile ones, 3 passes on bits [0,24)
+static int run_segments(thrs_sorter* s, uint32_t n)
+{
+    std::vector<uint32_t> k(n), v(n);
+    for (uint32_t i = 0; i < n; ++i) { k[i] = (uint32_t)mix(i) & 0x00ffffffu; v[i] = i; }
+    std::vector<uint64_t> seg = {0, 1, 1, n / 7, n / 3, n / 3 + 11, n / 2, n};
+    const uint32_t nseg = (uint32_t)seg.size() - 1;
+    void *dk, *dv, *dt;
+    const uint64_t tb = thrs_segments_temp_bytes(s, n, nseg, 1);
+    CU(cudaMalloc(&dk, 4ull * n)); CU(cudaMalloc(&dv, 4ull * n)); CU(cudaMalloc(&dt, tb));
+    CU(cudaMemset(dt, 0xA5, tb));
+    CU(cudaMemcpy(dk, k.data(), 4ull * n, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(dv, v.data(), 4ull * n, cudaMemcpyHostToDevice));
+    TH(thrs_sort_segments_pairs(s, dk, dv, seg.data(), nseg, dt, 0, 24, 0));
+    CU(cudaDeviceSynchronize());
+    std::vector<uint32_t> ok(n), ov(n);
+    CU(cudaMemcpy(ok.data(), dk, 4ull * n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(ov.data(), dv, 4ull * n, cudaMemcpyDeviceToHost));
+    int bad = 0;
+    for (uint32_t q = 0; q < nseg && !bad; ++q) {
+        std::vector<std::pair<uint32_t, uint32_t>> p;
+        for (uint64_t i = seg[q]; i < seg[q + 1]; ++i) p.push_back({k[i], v[i]});
+        std::stable_sort(p.begin(), p.end(), [](const std::pair<uint32_t, uint32_t>& a, const std::pair<uint32_t, uint32_t>& b) { return a.first < b.first; });
+        for (uint64_t i = seg[q]; i < seg[q + 1] && !bad; ++i) bad = ok[i] != p[i - seg[q]].first || ov[i] != p[i - seg[q]].second;
+    }
+    printf("[%s] segmented sort (%u segments) n=%u\n", bad ? "FAILED" : "  OK  ", nseg, n);
+    cudaFree(dk); cudaFree(dv); cudaFree(dt);
+    return bad;
+}
+
+// the exchange layer with two ranks on this one device (thrs_mg_*: peer windows = plain pointers)
+static int run_exchange(uint32_t n)
+{
+    thrs_config cfg;
+    thrs_config_default(&cfg);
+    int ids[2] = {0, 0};
+    thrs_mg* m;
+    if (thrs_mg_create(2, ids, &cfg, &m)) { printf("thrs_mg_create: %s\n", thrs_mg_last_error()); return 1; }
+    const uint64_t cnt[2] = {n, n / 2 + 3};
+    std::vector<uint32_t> k[2], v[2];
+    void *dk[2], *dv[2], *ok[2], *ov[2];
+    uint64_t cap[2], got[2];
+    for (int g = 0; g < 2; ++g) {
+        k[g].resize(cnt[g]); v[g].resize(cnt[g]);
+        for (uint64_t i = 0; i < cnt[g]; ++i) { k[g][i] = (uint32_t)mix(i * 2 + g); v[g][i] = (uint32_t)(i + (g ? cnt[0] : 0)); }
+        cap[g] = cnt[0] + cnt[1];
+        CU(cudaMalloc(&dk[g], 4 * cnt[g])); CU(cudaMalloc(&dv[g], 4 * cnt[g]));
+        CU(cudaMalloc(&ok[g], 4 * cap[g])); CU(cudaMalloc(&ov[g], 4 * cap[g]));
+        CU(cudaMemcpy(dk[g], k[g].data(), 4 * cnt[g], cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(dv[g], v[g].data(), 4 * cnt[g], cudaMemcpyHostToDevice));
+    }
+    int rc = thrs_mg_sort_pairs(m, dk, dv, cnt, ok, ov, cap, got);
+    if (rc) { printf("thrs_mg_sort_pairs: %s\n", thrs_mg_last_error()); return 1; }
+    std::vector<std::pair<uint32_t, uint32_t>> p;
+    for (int g = 0; g < 2; ++g) for (uint64_t i = 0; i < cnt[g]; ++i) p.push_back({k[g][i], v[g][i]});
+    std::stable_sort(p.begin(), p.end(), [](const std::pair<uint32_t, uint32_t>& a, const std::pair<uint32_t, uint32_t>& b) { return a.first < b.first; });
+    int bad = got[0] + got[1] != p.size();
+    uint64_t j = 0;
+    for (int g = 0; g < 2 && !bad; ++g) {
+        std::vector<uint32_t> gk(got[g]), gv(got[g]);
+        CU(cudaMemcpy(gk.data(), ok[g], 4 * got[g], cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(gv.data(), ov[g], 4 * got[g], cudaMemcpyDeviceToHost));
+        for (uint64_t i = 0; i < got[g] && !bad; ++i, ++j) bad = gk[i] != p[j].first || gv[i] != p[j].second;
+    }
+    printf("[%s] exchange layer, 2 ranks on one device n=%u+%u\n", bad ? "FAILED" : "  OK  ", (unsigned)cnt[0], (unsigned)cnt[1]);
+    thrs_mg_destroy(m);
+    for (int g = 0; g < 2; ++g) { cudaFree(dk[g]); cudaFree(dv[g]); cudaFree(ok[g]); cudaFree(ov[g]); }
+    return bad;
+}
+
 int main(int argc, char** argv)
 {
     const uint32_t n_full = argc > 1 ? (uint32_t)strtoull(argv[1], 0, 10) : (1u << 21) + 12345u;
@@ -112,8 +183,10 @@ int main(int argc, char** argv)
         bad += run_sort(s, n_full, false, "full tile");
         bad += run_sort(s, n_full, true, "full tile, 16 values per digit", 0x0f0f0f0fu);
         bad += run_scatter(s, n_full);
+        bad += run_segments(s, n_full);
         thrs_destroy(s);
     }
+    bad += run_exchange(n_full);
     printf("%d failed\n", bad);
     return bad ? 1 : 0;
 }

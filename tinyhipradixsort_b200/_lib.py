@@ -97,6 +97,22 @@ SIGNATURES = {
     "thrs_sort_segments_ex": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                              ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int,
                                              ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]),
+    "thrs_partition_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                            ctypes.c_void_p]),
+    "thrs_xchg_create": (ctypes.c_int, [ctypes.POINTER(thrs_config), ctypes.c_int, ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64,
+                                        ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]),
+    "thrs_xchg_destroy": (None, [ctypes.c_void_p]),
+    "thrs_xchg_window": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_uint64)]),
+    "thrs_xchg_set_peers": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "thrs_xchg_begin": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]),
+    "thrs_xchg_finish": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_void_p),
+                                        ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]),
+    "thrs_xchg_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64),
+                                       ctypes.POINTER(ctypes.c_uint32), ctypes.POINTER(ctypes.c_uint32)]),
+    "thrs_xchg_plan": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_int32),
+                                      ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_int32)]),
+    "thrs_xchg_last_error": (ctypes.c_char_p, []),
     "thrs_get_ranking_check": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_uint64)]),
 }
 

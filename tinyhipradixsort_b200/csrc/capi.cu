@@ -90,6 +90,13 @@ struct thrs_sorter {
     void* ws_temp = nullptr;
     uint64_t ws_keys_bytes = 0, ws_vals_bytes = 0, ws_temp_bytes = 0;
     cudaStream_t ws_stream = nullptr;
+    // pinned staging ring for the segment tables of thrs_sort_segments_* (a pageable source would make
+    // cudaMemcpyAsync wait for the stream first, and callers enqueue behind cross-GPU waits)
+    static constexpr int SEG_RING = 64;
+    std::mutex seg_mu;
+    uint32_t* seg_host = nullptr; // SEG_RING tables
+    cudaEvent_t seg_ev[SEG_RING] = {};
+    int seg_next = 0;
     // optional per-stage CUDA-event timing (thrs_profile_enable); one sort in flight when on
     bool profiling = false;
     cudaEvent_t ev[MAX_PASSES * MAX_PARTS + 4] = {};
@@ -163,6 +170,9 @@ void thrs_destroy(thrs_sorter* s)
     if (s->ws_stream) cudaStreamDestroy(s->ws_stream);
     for (cudaEvent_t e : s->ev)
         if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : s->seg_ev)
+        if (e) cudaEventDestroy(e);
+    if (s->seg_host) cudaFreeHost(s->seg_host);
     delete s;
 }
 
@@ -202,8 +212,15 @@ int thrs_temp_bytes(const thrs_sorter* s, uint32_t n, thrs_temp_def* out)
     return THRS_OK;
 }
 
+struct PassOutput { // where a one-pass partition leaves its result (thrs_partition_pairs); null = ordinary sort
+    void* keys = nullptr;
+    void* values = nullptr;
+    uint32_t* counts = nullptr;   // device, 256 words: the digit histogram
+    cudaEvent_t counts_ready = nullptr; // recorded on the stream once `counts` is written
+};
 static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys, void* values, bool pairs, uint32_t n,
-                     void* temp, int start_bits, int passes, cudaStream_t stream, bool allow_profile);
+                     void* temp, int start_bits, int passes, cudaStream_t stream, bool allow_profile,
+                     const PassOutput* out = nullptr);
 static int run_production_rank_check(thrs_sorter* s, DeviceState& ds);
 
 // Device facts + opt-in to large dynamic shared memory + ranking checks, once per (sorter, device).
@@ -409,7 +426,7 @@ static int sort_impl(thrs_sorter* s, void* keys, void* values, bool pairs, uint3
 
 // The launches of one sort.  Reads the sorter, writes nothing to it unless profiling is on.
 static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys, void* values, bool pairs, uint32_t n,
-                     void* temp, int start_bits, int passes, cudaStream_t stream, bool allow_profile)
+                     void* temp, int start_bits, int passes, cudaStream_t stream, bool allow_profile, const PassOutput* out)
 {
     const bool profiling = allow_profile && s->profiling;
     const int vslot = pairs ? s->vslot : 0;
@@ -431,7 +448,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
     };
 
     // small inputs: the whole sort in one block, in place, one launch, no scratch (small_sort.cuh)
-    if (n <= SMALL_SORT_MAX && !s->force_multiblock) {
+    if (!out && n <= SMALL_SORT_MAX && !s->force_multiblock) {
         for (int i = 0; i < 3; ++i) CUDA_TRY(mark(), "profile event");
         CUDA_TRY(s->table->small[vslot](keys, values, n, (uint32_t)start_bits, passes, stream), "small_sort_kernel launch");
         ++g_launches;
@@ -441,7 +458,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
     }
 
     // up to 8 x 4 096 items: one launch of one thread-block cluster, in place, no scratch (cluster_sort.cuh)
-    if (s->cluster_path && !s->force_multiblock && (uint64_t)n <= (uint64_t)ds.cluster_blocks[vslot] * SMALL_SORT_MAX) {
+    if (!out && s->cluster_path && !s->force_multiblock && (uint64_t)n <= (uint64_t)ds.cluster_blocks[vslot] * SMALL_SORT_MAX) {
         int blocks = 2;
         while ((uint64_t)blocks * SMALL_SORT_MAX < n) blocks *= 2;
         for (int i = 0; i < 3; ++i) CUDA_TRY(mark(), "profile event");
@@ -456,8 +473,8 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
     thrs_temp_def def;
     thrs_temp_bytes(s, n, &def);
     Scratch sc{static_cast<uint32_t*>(temp)};
-    char* key_out = static_cast<char*>(temp) + def.pSumBuffer;
-    char* val_out = key_out + def.keyOutBuffer;
+    char* key_out = out ? static_cast<char*>(out->keys) : static_cast<char*>(temp) + def.pSumBuffer;
+    char* val_out = out ? static_cast<char*>(out->values) : key_out + def.keyOutBuffer;
 
     const bool mid = n <= s->mid_max;
     const uint32_t tile = mid ? s->table->tile_items_mid[vslot] : s->table->tile_items[fast][vslot];
@@ -470,7 +487,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
 
     // zero: histograms, bases, tickets, counters and the status rows of the passes we run
     const size_t clear_bytes = 4ull * (Scratch::CONTROL_WORDS + (uint64_t)passes * Scratch::pass_words(tiles_total));
-    const bool pdl = s->pdl && !profiling;
+    const bool pdl = s->pdl && !profiling && !(out && out->counts); // a copy sits between the histogram and the pass then
     CUDA_TRY(launch_zero(temp, clear_bytes, ds.sm_count, stream), "zero_kernel launch");
     ++g_launches;
     CUDA_TRY(mark(), "profile event");
@@ -485,6 +502,10 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
                  "histogram_kernel launch");
         ++g_launches;
         CUDA_TRY(mark(), "profile event");
+        if (out && out->counts) {
+            CUDA_TRY(cudaMemcpyAsync(out->counts, sc.hist(), 4ull * RADIX, cudaMemcpyDeviceToDevice, stream), "copy histogram");
+            if (out->counts_ready) CUDA_TRY(cudaEventRecord(out->counts_ready, stream), "cudaEventRecord");
+        }
     }
 
     char* k_in = static_cast<char*>(keys);
@@ -521,7 +542,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
         char* t = k_in; k_in = k_out; k_out = t;
         t = v_in; v_in = v_out; v_out = t;
     }
-    if (passes & 1) {
+    if ((passes & 1) && !out) {
         // result must land in the caller's buffers (hpp:936-943); on the caller's stream
         CUDA_TRY(cudaMemcpyAsync(keys, key_out, (size_t)s->kbytes * n, cudaMemcpyDeviceToDevice, stream),
                  "copy-back keys");
@@ -530,7 +551,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
                      "copy-back values");
         CUDA_TRY(mark(), "profile event");
     }
-    profile_done(passes, parts, (passes & 1) != 0);
+    profile_done(passes, parts, (passes & 1) != 0 && !out);
     return THRS_OK;
 }
 
@@ -580,6 +601,34 @@ int thrs_sort_pairs(thrs_sorter* s, void* keys, void* values, uint32_t n, void* 
                     void* stream)
 {
     return sort_impl(s, keys, values, true, n, temp, start_bits, end_bits, static_cast<cudaStream_t>(stream));
+}
+
+int thrs_partition_pairs(thrs_sorter* s, const void* keys, const void* values, uint32_t n, void* temp, void* out_keys,
+                         void* out_values, int bit, uint32_t* counts_out, void* counts_ready_event, void* stream)
+{
+    g_launches = 0;
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_partition_pairs: NULL sorter");
+    if (bit < 0 || bit >= s->kbytes * 8) return fail(THRS_ERR_BIT_RANGE, "thrs_partition_pairs: bit outside the key");
+    if (n == 0) {
+        if (counts_out) CUDA_TRY(cudaMemsetAsync(counts_out, 0, 4ull * RADIX, static_cast<cudaStream_t>(stream)), "cudaMemsetAsync");
+        if (counts_out && counts_ready_event)
+            CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(counts_ready_event), static_cast<cudaStream_t>(stream)), "cudaEventRecord");
+        return THRS_OK;
+    }
+    if (!keys || !values || !temp || !out_keys || !out_values) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_partition_pairs: NULL buffer");
+    if (((uintptr_t)keys % s->kbytes) != 0 || ((uintptr_t)out_keys % s->kbytes) != 0 || ((uintptr_t)temp % 16) != 0 ||
+        ((uintptr_t)values % s->vbytes) != 0 || ((uintptr_t)out_values % s->vbytes) != 0)
+        return fail(THRS_ERR_ALIGNMENT, "thrs_partition_pairs: misaligned buffer");
+    const DeviceState* ds = nullptr;
+    int prc = prepare_device(s, &ds);
+    if (prc) return prc;
+    PassOutput out;
+    out.keys = out_keys;
+    out.values = out_values;
+    out.counts = counts_out;
+    out.counts_ready = static_cast<cudaEvent_t>(counts_ready_event);
+    return sort_core(s, *ds, resolve_fast(s, *ds), const_cast<void*>(keys), const_cast<void*>(values), true, n, temp, bit, 1,
+                     static_cast<cudaStream_t>(stream), false, &out);
 }
 
 int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, int start_bit, uint32_t* counts_out, void* temp,
@@ -733,12 +782,24 @@ int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_ke
     const int vslot = pairs ? s->vslot : 0;
     const uint32_t tile = s->table->tile_items[fast][vslot];
 
-    std::vector<uint32_t> table(SegScratch::TABLE_WORDS);
     for (uint32_t first_seg = 0; first_seg < nseg; first_seg += MAX_SEGMENTS) {
         const uint32_t ns = nseg - first_seg < (uint32_t)MAX_SEGMENTS ? nseg - first_seg : (uint32_t)MAX_SEGMENTS;
+        // a pinned slot for this batch's table (reused SEG_RING batches later, after its upload completed)
+        uint32_t* table = nullptr;
+        cudaEvent_t table_ev = nullptr;
+        {
+            std::lock_guard<std::mutex> lock(s->seg_mu);
+            if (!s->seg_host) CUDA_TRY(cudaMallocHost(&s->seg_host, (size_t)thrs_sorter::SEG_RING * SegScratch::TABLE_WORDS * 4), "cudaMallocHost(segment tables)");
+            const int slot = s->seg_next;
+            s->seg_next = (slot + 1) % thrs_sorter::SEG_RING;
+            if (!s->seg_ev[slot]) CUDA_TRY(cudaEventCreateWithFlags(&s->seg_ev[slot], cudaEventDisableTiming), "cudaEventCreate");
+            else CUDA_TRY(cudaEventSynchronize(s->seg_ev[slot]), "cudaEventSynchronize(segment table slot)");
+            table = s->seg_host + (size_t)slot * SegScratch::TABLE_WORDS;
+            table_ev = s->seg_ev[slot];
+        }
         // table of this batch: virtual tile ranges start at whole groups
-        std::fill(table.begin(), table.end(), 0u);
-        uint32_t* vt_first = table.data() + SEG_HEADER;
+        std::fill(table, table + SegScratch::TABLE_WORDS, 0u);
+        uint32_t* vt_first = table + SEG_HEADER;
         uint32_t* begin = vt_first + (MAX_SEGMENTS + 1);
         uint32_t* count = begin + (MAX_SEGMENTS + 1);
         uint64_t vt = 0;
@@ -753,7 +814,10 @@ int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_ke
         begin[ns] = (uint32_t)seg_begin[first_seg + ns];
         table[0] = ns;
         table[1] = (uint32_t)vt;
-        if (begin[ns] == begin[0]) continue; // only empty segments
+        if (begin[ns] == begin[0]) { // only empty segments
+            CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
+            continue;
+        }
         const uint64_t vtiles = vt, vgroups = vt / GROUP_TILES + 1;
         if (4ull * SegScratch::words(vtiles, ns, passes) > scratch_bytes)
             return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: scratch too small (thrs_segments_scratch_bytes)");
@@ -764,7 +828,8 @@ int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_ke
         uint32_t* d_base = d_hist + (uint64_t)ns * passes * RADIX;
         uint32_t* d_pass = d_base + (uint64_t)ns * passes * RADIX;
         const uint64_t pass_words = (vtiles + 2 * vgroups) * RADIX;
-        CUDA_TRY(cudaMemcpyAsync(d_table, table.data(), 4ull * SegScratch::TABLE_WORDS, cudaMemcpyHostToDevice, stream), "upload segment table");
+        CUDA_TRY(cudaMemcpyAsync(d_table, table, 4ull * SegScratch::TABLE_WORDS, cudaMemcpyHostToDevice, stream), "upload segment table");
+        CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
         // zero: tickets, histograms (bases are overwritten), status rows of the passes
         CUDA_TRY(launch_zero(d_ticket, 4ull * (SegScratch::TICKET_WORDS + (uint64_t)ns * passes * RADIX), ds->sm_count, stream), "zero_kernel launch");
         CUDA_TRY(launch_zero(d_pass, 4ull * passes * pass_words, ds->sm_count, stream), "zero_kernel launch");

@@ -1,0 +1,450 @@
+// capi_xchg.cu — the exchange layer of the multi-GPU sort (include/thrs_b200.h, thrs_xchg_*): one
+// context per rank (= per GPU), for hosts that run one process per GPU (windows opened through CUDA IPC)
+// as well as for one process that drives several devices (thrs_mg_*, capi_mg.cu).  The reference has no
+// multi-GPU path (single device: unittest.cpp:22,51); this follows SURVEY.md 8(e) and the round-1
+// verdict: the exchange is ONE of the radix passes, not an extra one, and it overlaps the local sort.
+//
+//   begin   top-digit histogram of the rank's slice + ONE stable out-of-place pass on the top digit
+//           (thrs_partition_pairs: this IS the last radix pass of the sort) into the send buffers;
+//           meanwhile a side stream pushes the 256 counts into every rank's window with the copy
+//           engines (no NCCL, no SMs) and reads the gathered table back to the host
+//   finish  splitters on digit boundaries (equal keys never straddle ranks); every (digit, source) chunk
+//           is copied by the copy engines straight into the owner's receive buffer, laid out
+//           DIGIT-MAJOR / SOURCE-MINOR, so that what a rank receives is already partitioned by the top
+//           digit with ties in global input order; chunks travel group by group (a group = a few
+//           consecutive digits of one owner), each followed by a 4-byte flag copy on the same stream;
+//           the owner's stream waits for a group's flags with cuStreamWaitValue32 (no spinning SM) and
+//           runs a SEGMENTED sort (thrs_sort_segments_ex, one segment per digit) on the remaining low
+//           bits of that group while the later groups are still in flight.
+// Concatenating the ranks' outputs is exactly std::stable_sort of the concatenated inputs.
+// Built from the public single-GPU entry points plus the CUDA runtime; flags are epoch numbers, so
+// nothing is ever reset between sorts.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <new>
+#include <vector>
+#include "../../include/thrs_b200.h"
+
+namespace {
+
+thread_local char g_x_err[512];
+int x_fail(int code, const char* what, cudaError_t e = cudaSuccess)
+{
+    if (e != cudaSuccess) snprintf(g_x_err, sizeof(g_x_err), "%s: %s", what, cudaGetErrorString(e));
+    else snprintf(g_x_err, sizeof(g_x_err), "%s", what);
+    return code;
+}
+#define X_CUDA(x, what) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) { cudaGetLastError(); return x_fail(THRS_ERR_CUDA, what, e__); } } while (0)
+#define X_THRS(x) do { int rc__ = (x); if (rc__ != THRS_OK) { snprintf(g_x_err, sizeof(g_x_err), "%s", thrs_last_error()); return rc__; } } while (0)
+
+constexpr int MAX_WORLD = 8;
+constexpr int MAX_GROUPS = 16;
+constexpr int FLAG_SLOTS = MAX_GROUPS + 1; // [MAX_GROUPS] = "counts have landed"
+inline uint64_t up256(uint64_t x) { return (x + 255ull) & ~255ull; }
+
+// cuStreamWaitValue32 through the runtime's driver entry point (no link-time dependency on libcuda)
+typedef int (*WaitValue32Fn)(cudaStream_t, unsigned long long, uint32_t, unsigned int);
+WaitValue32Fn wait_value32()
+{
+    static WaitValue32Fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        const char* mode = getenv("THRS_XCHG_WAIT");
+        if (!(mode && !strcmp(mode, "kernel"))) {
+            void* p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) == cudaSuccess && p &&
+                q == cudaDriverEntryPointSuccess)
+                fn = reinterpret_cast<WaitValue32Fn>(p);
+            else cudaGetLastError();
+        }
+    }
+    return fn;
+}
+
+// fallback when stream memory operations are unavailable: one warp polls up to 32 flags
+__global__ void wait_flags_kernel(const volatile uint32_t* flags, int stride_words, int count, uint32_t epoch)
+{
+    if ((int)threadIdx.x < count) {
+        const volatile uint32_t* f = flags + (size_t)threadIdx.x * stride_words;
+        while ((int32_t)(*f - epoch) < 0) __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
+} // namespace
+
+struct thrs_xchg {
+    thrs_config cfg;
+    int rank = 0, world = 1, groups = 4;
+    int device = 0;
+    int kbytes = 4, vbytes = 4, key_bits = 32;
+    thrs_sorter* sorter = nullptr;
+    uint64_t capacity = 0;  // items the receive buffers hold
+    uint64_t max_local = 0; // items a local slice may have
+    // window: [flags | counts | recv keys | recv values] — the only memory other ranks write
+    char* window = nullptr;
+    uint64_t window_bytes = 0, off_counts = 0, off_keys = 0, off_vals = 0;
+    std::vector<char*> peer; // every rank's window as seen from this process (own one included)
+    // private buffers
+    char *send_keys = nullptr, *send_vals = nullptr, *alt_keys = nullptr, *alt_vals = nullptr, *part_temp = nullptr,
+         *seg_scratch = nullptr;
+    uint64_t seg_scratch_bytes = 0;
+    uint32_t* d_counts = nullptr; // 256
+    uint32_t* d_epoch = nullptr;  // [2]
+    uint32_t* h_epoch = nullptr;  // pinned [2]
+    uint32_t* h_counts = nullptr; // pinned [world][256]
+    cudaStream_t side = nullptr;
+    cudaStream_t copy[MAX_WORLD] = {};
+    cudaEvent_t ev_counts = nullptr, ev_part = nullptr, ev_host = nullptr, ev_copy[MAX_WORLD] = {};
+    uint32_t epoch = 0;
+    uint64_t n_local = 0;
+    bool began = false;
+    // what the last finish computed (introspection for benchmarks and tests)
+    uint64_t last_recv = 0, last_sent_remote_bytes = 0;
+    uint32_t last_launches = 0, last_copies = 0;
+
+    uint32_t* flag_ptr(char* win, int parity, int src, int slot) const
+    {
+        return reinterpret_cast<uint32_t*>(win) + ((size_t)parity * MAX_WORLD + src) * FLAG_SLOTS + slot;
+    }
+    uint32_t* counts_ptr(char* win, int parity, int src) const
+    {
+        return reinterpret_cast<uint32_t*>(win + off_counts) + ((size_t)parity * MAX_WORLD + src) * 256;
+    }
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = 0;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
+    ~DeviceGuard() { int cur = 0; cudaGetDevice(&cur); if (cur != prev) cudaSetDevice(prev); }
+};
+
+int wait_flags(thrs_xchg* x, cudaStream_t stream, int parity, int slot)
+{
+    if (WaitValue32Fn fn = wait_value32()) {
+        for (int src = 0; src < x->world; ++src) {
+            const int rc = fn(stream, (unsigned long long)(uintptr_t)x->flag_ptr(x->window, parity, src, slot), x->epoch, 0u /* GEQ */);
+            if (rc != 0) return x_fail(THRS_ERR_CUDA, "cuStreamWaitValue32 failed (set THRS_XCHG_WAIT=kernel to poll from a kernel)");
+        }
+        return THRS_OK;
+    }
+    wait_flags_kernel<<<1, 32, 0, stream>>>(x->flag_ptr(x->window, parity, 0, slot), FLAG_SLOTS, x->world, x->epoch);
+    X_CUDA(cudaGetLastError(), "wait_flags_kernel launch");
+    return THRS_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* thrs_xchg_last_error(void) { return g_x_err; }
+
+// Host-only planning, shared by every rank (all see the same table): owner of each top-digit bucket,
+// items every rank receives, and the group a bucket travels in.  counts[src * 256 + digit], 64-bit.
+int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner_of_digit, uint64_t* recv_totals,
+                   int32_t* group_of_digit)
+{
+    if (world < 1 || world > MAX_WORLD || !counts || !owner_of_digit || !recv_totals)
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_plan: bad argument");
+    if (groups < 1) groups = 1;
+    if (groups > MAX_GROUPS) groups = MAX_GROUPS;
+    uint64_t tot[256], total = 0;
+    for (int d = 0; d < 256; ++d) {
+        tot[d] = 0;
+        for (int s = 0; s < world; ++s) tot[d] += counts[(size_t)s * 256 + d];
+        total += tot[d];
+    }
+    // bucket d -> rank floor(world * items_before(d) / total): monotone in d, buckets stay whole
+    uint64_t before = 0;
+    for (int r = 0; r < world; ++r) recv_totals[r] = 0;
+    for (int d = 0; d < 256; ++d) {
+        uint64_t o = total ? (uint64_t)((unsigned __int128)before * (uint64_t)world / total) : 0;
+        if (o > (uint64_t)world - 1) o = (uint64_t)world - 1;
+        owner_of_digit[d] = (int32_t)o;
+        recv_totals[o] += tot[d];
+        before += tot[d];
+    }
+    if (group_of_digit) {
+        // inside an owner: bucket -> group floor(groups * items_before_in_owner / owner_total), same rule
+        uint64_t b = 0;
+        int cur = -1;
+        for (int d = 0; d < 256; ++d) {
+            const int o = owner_of_digit[d];
+            if (o != cur) { cur = o; b = 0; }
+            uint64_t g = recv_totals[o] ? (uint64_t)((unsigned __int128)b * (uint64_t)groups / recv_totals[o]) : 0;
+            if (g > (uint64_t)groups - 1) g = (uint64_t)groups - 1;
+            group_of_digit[d] = (int32_t)g;
+            b += tot[d];
+        }
+    }
+    return THRS_OK;
+}
+
+void thrs_xchg_destroy(thrs_xchg* x)
+{
+    if (!x) return;
+    DeviceGuard g(x->device);
+    cudaDeviceSynchronize();
+    if (x->window) cudaFree(x->window);
+    for (char* p : {x->send_keys, x->send_vals, x->alt_keys, x->alt_vals, x->part_temp, x->seg_scratch})
+        if (p) cudaFree(p);
+    if (x->d_counts) cudaFree(x->d_counts);
+    if (x->d_epoch) cudaFree(x->d_epoch);
+    if (x->h_epoch) cudaFreeHost(x->h_epoch);
+    if (x->h_counts) cudaFreeHost(x->h_counts);
+    if (x->side) cudaStreamDestroy(x->side);
+    for (int r = 0; r < MAX_WORLD; ++r) {
+        if (x->copy[r]) cudaStreamDestroy(x->copy[r]);
+        if (x->ev_copy[r]) cudaEventDestroy(x->ev_copy[r]);
+    }
+    for (cudaEvent_t e : {x->ev_counts, x->ev_part, x->ev_host})
+        if (e) cudaEventDestroy(e);
+    if (x->sorter) thrs_destroy(x->sorter);
+    cudaGetLastError();
+    delete x;
+}
+
+int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_local_items, uint64_t capacity_items,
+                     int groups, thrs_xchg** out)
+{
+    if (!cfg || !out) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_create: NULL argument");
+    if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world)
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_create: 1..8 ranks (one NVSwitch box)");
+    if (cfg->value_type != THRS_VALUE_U32 && cfg->value_type != THRS_VALUE_U64)
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_create: 4- and 8-byte values only");
+    if (max_local_items >= (1ull << 32) || capacity_items >= (1ull << 32))
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_create: a rank's slice and share must stay below 2^32 items");
+    thrs_xchg* x = new (std::nothrow) thrs_xchg();
+    if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_create: out of host memory");
+    x->cfg = *cfg;
+    x->rank = rank;
+    x->world = world;
+    x->groups = groups < 1 ? 1 : (groups > MAX_GROUPS ? MAX_GROUPS : groups);
+    x->kbytes = (cfg->key_type == THRS_KEY_U32 || cfg->key_type == THRS_KEY_F32) ? 4 : 8;
+    x->vbytes = cfg->value_type == THRS_VALUE_U32 ? 4 : 8;
+    x->key_bits = x->kbytes * 8;
+    x->capacity = capacity_items ? capacity_items : 1;
+    x->max_local = max_local_items ? max_local_items : 1;
+    x->peer.assign(world, nullptr);
+    cudaError_t e = cudaGetDevice(&x->device);
+    int rc = THRS_OK;
+    if (e != cudaSuccess) rc = x_fail(THRS_ERR_NO_DEVICE, "thrs_xchg_create: no CUDA device", e);
+    if (rc == THRS_OK && (rc = thrs_create(cfg, &x->sorter)) != THRS_OK) snprintf(g_x_err, sizeof(g_x_err), "%s", thrs_last_error());
+    if (rc == THRS_OK) {
+        const uint64_t flag_bytes = up256(2ull * MAX_WORLD * FLAG_SLOTS * 4);
+        x->off_counts = flag_bytes;
+        x->off_keys = x->off_counts + up256(2ull * MAX_WORLD * 256 * 4);
+        x->off_vals = x->off_keys + up256(x->capacity * x->kbytes);
+        x->window_bytes = x->off_vals + up256(x->capacity * x->vbytes);
+        thrs_temp_def def;
+        thrs_temp_bytes(x->sorter, (uint32_t)x->max_local, &def);
+        x->seg_scratch_bytes = thrs_segments_scratch_bytes(x->sorter, x->capacity, 256);
+        e = cudaMalloc(&x->window, x->window_bytes);
+        if (e == cudaSuccess) e = cudaMemset(x->window, 0, x->off_keys);
+        if (e == cudaSuccess) e = cudaMalloc(&x->send_keys, up256(x->max_local * x->kbytes));
+        if (e == cudaSuccess) e = cudaMalloc(&x->send_vals, up256(x->max_local * x->vbytes));
+        if (e == cudaSuccess) e = cudaMalloc(&x->alt_keys, up256(x->capacity * x->kbytes));
+        if (e == cudaSuccess) e = cudaMalloc(&x->alt_vals, up256(x->capacity * x->vbytes));
+        if (e == cudaSuccess) e = cudaMalloc(&x->part_temp, def.pSumBuffer);
+        if (e == cudaSuccess) e = cudaMalloc(&x->seg_scratch, x->seg_scratch_bytes);
+        if (e == cudaSuccess) e = cudaMalloc(&x->d_counts, 1024);
+        if (e == cudaSuccess) e = cudaMalloc(&x->d_epoch, 8);
+        if (e == cudaSuccess) e = cudaMallocHost(&x->h_epoch, 8);
+        if (e == cudaSuccess) e = cudaMallocHost(&x->h_counts, (size_t)world * 1024);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->side, cudaStreamNonBlocking);
+        for (int r = 0; r < world && e == cudaSuccess; ++r) {
+            e = cudaStreamCreateWithFlags(&x->copy[r], cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_copy[r], cudaEventDisableTiming);
+        }
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_counts, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_part, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_host, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { cudaGetLastError(); rc = x_fail(THRS_ERR_CUDA, "thrs_xchg_create: buffers", e); }
+    }
+    if (rc != THRS_OK) { thrs_xchg_destroy(x); return rc; }
+    x->peer[rank] = x->window;
+    *out = x;
+    return THRS_OK;
+}
+
+int thrs_xchg_window(thrs_xchg* x, void** base, uint64_t* bytes)
+{
+    if (!x || !base) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_window: NULL argument");
+    *base = x->window;
+    if (bytes) *bytes = x->window_bytes;
+    return THRS_OK;
+}
+
+int thrs_xchg_set_peers(thrs_xchg* x, void* const* window_bases)
+{
+    if (!x || !window_bases) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_set_peers: NULL argument");
+    for (int r = 0; r < x->world; ++r) {
+        if (!window_bases[r]) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_set_peers: NULL window");
+        x->peer[r] = (r == x->rank) ? x->window : static_cast<char*>(window_bases[r]);
+    }
+    return THRS_OK;
+}
+
+int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t n, void* stream_)
+{
+    if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_begin: NULL context");
+    if (n > x->max_local) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_begin: slice larger than max_local_items");
+    for (int r = 0; r < x->world; ++r)
+        if (!x->peer[r]) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_begin: thrs_xchg_set_peers first");
+    DeviceGuard g(x->device);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ++x->epoch;
+    const int par = (int)(x->epoch & 1u);
+    x->n_local = n;
+    x->h_epoch[par] = x->epoch;
+    X_CUDA(cudaMemcpyAsync(x->d_epoch + par, x->h_epoch + par, 4, cudaMemcpyHostToDevice, stream), "epoch upload");
+    // top-digit histogram -> d_counts (ev_counts), then the stable pass on the top digit into the send buffers
+    X_THRS(thrs_partition_pairs(x->sorter, keys, values, (uint32_t)n, x->part_temp, x->send_keys, x->send_vals, x->key_bits - 8,
+                                x->d_counts, x->ev_counts, stream));
+    x->last_launches = (uint32_t)thrs_last_launch_count();
+    x->last_copies = 0;
+    X_CUDA(cudaEventRecord(x->ev_part, stream), "cudaEventRecord");
+    // side stream: push the counts to everyone (copy engines), then collect everyone's and bring them to the host
+    X_CUDA(cudaStreamWaitEvent(x->side, x->ev_counts, 0), "cudaStreamWaitEvent");
+    for (int i = 0; i < x->world; ++i) {
+        const int r = (x->rank + i) % x->world;
+        X_CUDA(cudaMemcpyAsync(x->counts_ptr(x->peer[r], par, x->rank), x->d_counts, 1024, cudaMemcpyDefault, x->side), "push counts");
+        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, x->rank, MAX_GROUPS), x->d_epoch + par, 4, cudaMemcpyDefault, x->side),
+               "push counts flag");
+    }
+    int rc = wait_flags(x, x->side, par, MAX_GROUPS);
+    if (rc) return rc;
+    for (int s = 0; s < x->world; ++s)
+        X_CUDA(cudaMemcpyAsync(x->h_counts + (size_t)s * 256, x->counts_ptr(x->window, par, s), 1024, cudaMemcpyDeviceToHost, x->side),
+               "read counts");
+    X_CUDA(cudaEventRecord(x->ev_host, x->side), "cudaEventRecord");
+    x->began = true;
+    return THRS_OK;
+}
+
+int thrs_xchg_finish(thrs_xchg* x, void* stream_, void** out_keys, void** out_values, uint64_t* out_count,
+                     uint64_t* needed_capacity)
+{
+    if (!x || !out_keys || !out_values || !out_count) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_finish: NULL argument");
+    if (!x->began) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_finish: thrs_xchg_begin first");
+    x->began = false;
+    DeviceGuard g(x->device);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank;
+    X_CUDA(cudaEventSynchronize(x->ev_host), "waiting for the gathered histograms");
+
+    std::vector<uint64_t> counts((size_t)P * 256);
+    for (size_t i = 0; i < counts.size(); ++i) counts[i] = x->h_counts[i];
+    int32_t owner[256], group[256];
+    uint64_t recv[MAX_WORLD];
+    thrs_xchg_plan(P, x->groups, counts.data(), owner, recv, group);
+    uint64_t need = 0;
+    for (int r = 0; r < P; ++r) need = recv[r] > need ? recv[r] : need;
+    if (needed_capacity) *needed_capacity = need;
+    if (need > x->capacity) {
+        // every rank sees the same table and takes the same decision: nobody has copied anything yet
+        X_CUDA(cudaStreamWaitEvent(stream, x->ev_part, 0), "cudaStreamWaitEvent");
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_finish: a rank's share exceeds the receive capacity (see needed_capacity)");
+    }
+
+    // where my bucket d starts in my send buffers, and where my chunk of bucket d lands at its owner:
+    // digit-major / source-minor inside the owner's receive buffer
+    uint64_t send_base[257], land[256], tot[256];
+    send_base[0] = 0;
+    for (int d = 0; d < 256; ++d) send_base[d + 1] = send_base[d] + counts[(size_t)me * 256 + d];
+    {
+        uint64_t run = 0;
+        int cur = -1;
+        for (int d = 0; d < 256; ++d) {
+            if (owner[d] != cur) { cur = owner[d]; run = 0; }
+            uint64_t t = 0, mine = 0;
+            for (int s = 0; s < P; ++s) {
+                if (s == me) mine = run + t;
+                t += counts[(size_t)s * 256 + d];
+            }
+            land[d] = mine;
+            tot[d] = t;
+            run += t;
+        }
+    }
+
+    // ---- outgoing: group by group, one copy stream per destination, a flag after every group
+    uint64_t remote_bytes = 0;
+    for (int r = 0; r < P; ++r) X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_part, 0), "cudaStreamWaitEvent");
+    for (int gi = 0; gi < x->groups; ++gi) {
+        for (int i = 1; i <= P; ++i) {
+            const int r = (me + i) % P; // the own rank last: local copies are the cheapest to delay
+            for (int d = 0; d < 256; ++d) {
+                if (owner[d] != r || group[d] != gi) continue;
+                const uint64_t c = counts[(size_t)me * 256 + d];
+                if (!c) continue;
+                X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + land[d] * x->kbytes, x->send_keys + send_base[d] * x->kbytes,
+                                       c * x->kbytes, cudaMemcpyDefault, x->copy[r]), "bucket copy (keys)");
+                X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_vals + land[d] * x->vbytes, x->send_vals + send_base[d] * x->vbytes,
+                                       c * x->vbytes, cudaMemcpyDefault, x->copy[r]), "bucket copy (values)");
+                if (r != me) remote_bytes += c * (uint64_t)(x->kbytes + x->vbytes);
+                x->last_copies += 2;
+            }
+            X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDefault, x->copy[r]), "group flag");
+        }
+    }
+    for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
+
+    // ---- incoming: as soon as a group is complete, sort its buckets on the remaining low bits
+    int in_alt = 0;
+    bool any = false;
+    for (int gi = 0; gi < x->groups; ++gi) {
+        uint64_t seg_begin[257];
+        uint32_t nseg = 0;
+        uint64_t run = 0;
+        bool started = false;
+        for (int d = 0; d < 256; ++d) {
+            if (owner[d] != me) continue;
+            if (group[d] == gi) {
+                if (!started) { seg_begin[0] = run; started = true; }
+                seg_begin[++nseg] = run + tot[d];
+            }
+            run += tot[d];
+        }
+        int rc = wait_flags(x, stream, par, gi);
+        if (rc) return rc;
+        if (!nseg || seg_begin[nseg] == seg_begin[0]) continue;
+        int ia = 0;
+        X_THRS(thrs_sort_segments_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals,
+                                     x->seg_scratch, x->seg_scratch_bytes, seg_begin, nseg, 0, x->key_bits - 8, stream, &ia));
+        x->last_launches += (uint32_t)thrs_last_launch_count();
+        in_alt = ia;
+        any = true;
+    }
+    // the send buffers may be overwritten by the next sort only after my own copies have left
+    for (int r = 0; r < P; ++r) X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
+    (void)any;
+    *out_keys = in_alt ? x->alt_keys : x->window + x->off_keys;
+    *out_values = in_alt ? x->alt_vals : x->window + x->off_vals;
+    *out_count = recv[me];
+    x->last_recv = recv[me];
+    x->last_sent_remote_bytes = remote_bytes;
+    return THRS_OK;
+}
+
+int thrs_xchg_stats(thrs_xchg* x, uint64_t* received_items, uint64_t* sent_remote_bytes, uint32_t* kernel_launches,
+                    uint32_t* bucket_copies)
+{
+    if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_stats: NULL context");
+    if (received_items) *received_items = x->last_recv;
+    if (sent_remote_bytes) *sent_remote_bytes = x->last_sent_remote_bytes;
+    if (kernel_launches) *kernel_launches = x->last_launches;
+    if (bucket_copies) *bucket_copies = x->last_copies;
+    return THRS_OK;
+}
+
+} // extern "C"

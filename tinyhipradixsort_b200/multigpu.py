@@ -148,6 +148,113 @@ class CudaLocalOps:
             self.sorter.scatterPairs(keys, vals, n, self._temp(n), start_bit, bin_first, kd, vd, first)
 
 
+class CudaExchangeOps:
+    """Device work of one rank through the exchange layer of the C ABI (thrs_xchg_*, csrc/capi_xchg.cu):
+    the top-digit pass IS the sort's last radix pass, every (digit, source) chunk travels to its owner
+    with the copy engines, and the owner sorts the buckets it received with a segmented sort on the low
+    bits while later groups are still in flight.  torch.distributed is used ONCE per buffer size, to
+    pass the CUDA-IPC handles of the windows around; a sort itself involves no collective and no
+    Python-side arithmetic (histogram exchange, splitters and copy lists are C++)."""
+
+    def __init__(self, key="u32", value_bytes=4, descending=False, groups=4):
+        import ctypes
+
+        import torch
+
+        from . import _lib
+
+        self.torch, self.ct, self._lib = torch, ctypes, _lib.load()
+        self.key, self.vbytes, self.groups = key, value_bytes, groups
+        cfg = _lib.thrs_config()
+        self._lib.thrs_config_default(ctypes.byref(cfg))
+        cfg.key_type = {"u32": 0, "u64": 1, "f32": 2, "f64": 3}[key]
+        cfg.value_type = {4: 0, 8: 1}[value_bytes]
+        cfg.sort_order = 1 if descending else 0
+        self._cfg = cfg
+        self._x = None
+        self._opened = []
+        self.max_local = self.capacity = 0
+
+    def _err(self, what, rc):
+        return RuntimeError(f"{what} rc={rc}: {self._lib.thrs_xchg_last_error().decode()}")
+
+    def close(self):
+        from .radixsort import ipc_close
+
+        if self._x:
+            self.torch.cuda.synchronize()
+            for p in self._opened:
+                ipc_close(p)
+            self._opened = []
+            self._lib.thrs_xchg_destroy(self._x)
+            self._x = None
+
+    def reserve(self, dist, group, max_local, capacity):
+        """COLLECTIVE: (re)build the context for slices of up to max_local items and shares of up to
+        capacity items (identical numbers on every rank) and pass the window handles around."""
+        from .radixsort import ipc_export, ipc_open
+
+        ct = self.ct
+        self.close()
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        x = ct.c_void_p()
+        rc = self._lib.thrs_xchg_create(ct.byref(self._cfg), rank, world, int(max_local), int(capacity), self.groups, ct.byref(x))
+        if rc:
+            raise self._err("thrs_xchg_create", rc)
+        self._x = x
+        base, nbytes = ct.c_void_p(), ct.c_uint64()
+        self._lib.thrs_xchg_window(x, ct.byref(base), ct.byref(nbytes))
+        handles = [None] * world
+        dist.all_gather_object(handles, ipc_export(base.value), group=group)
+        bases = []
+        for r, h in enumerate(handles):
+            if r == rank:
+                bases.append(base.value)
+            else:
+                p = ipc_open(h)
+                self._opened.append(p)
+                bases.append(p)
+        arr = (ct.c_void_p * world)(*bases)
+        rc = self._lib.thrs_xchg_set_peers(x, arr)
+        if rc:
+            raise self._err("thrs_xchg_set_peers", rc)
+        self.max_local, self.capacity = int(max_local), int(capacity)
+        dist.barrier(group=group)
+
+    def begin(self, keys, vals, n, stream):
+        rc = self._lib.thrs_xchg_begin(self._x, keys.data_ptr(), vals.data_ptr(), int(n), stream)
+        if rc:
+            raise self._err("thrs_xchg_begin", rc)
+
+    def finish(self, stream):
+        """-> (keys_ptr, values_ptr, count, needed_capacity, ok)"""
+        ct = self.ct
+        ok_, ov_, cnt, need = ct.c_void_p(), ct.c_void_p(), ct.c_uint64(), ct.c_uint64()
+        rc = self._lib.thrs_xchg_finish(self._x, stream, ct.byref(ok_), ct.byref(ov_), ct.byref(cnt), ct.byref(need))
+        if rc and need.value <= self.capacity:
+            raise self._err("thrs_xchg_finish", rc)
+        return ok_.value, ov_.value, int(cnt.value), int(need.value), rc == 0
+
+    def stats(self):
+        ct = self.ct
+        recv, sent, launches, copies = ct.c_uint64(), ct.c_uint64(), ct.c_uint32(), ct.c_uint32()
+        self._lib.thrs_xchg_stats(self._x, ct.byref(recv), ct.byref(sent), ct.byref(launches), ct.byref(copies))
+        return {"received_items": int(recv.value), "sent_remote_bytes": int(sent.value), "kernel_launches": int(launches.value),
+                "bucket_copies": int(copies.value)}
+
+    def views(self, kptr, vptr, count, key_dtype, val_dtype):
+        torch = self.torch
+
+        class _Raw:
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+        ts = {torch.int32: "<i4", torch.int64: "<i8"}
+        k = torch.as_tensor(_Raw(kptr, max(count, 1), ts[key_dtype]), device="cuda")
+        v = torch.as_tensor(_Raw(vptr, max(count, 1), ts[val_dtype]), device="cuda")
+        return k[:count], v[:count]
+
+
 class DistributedRadixSort:
     """sort_pairs(keys, values) over all ranks of `group`.  Returns (keys_out, values_out, count):
     views of this rank's receive buffers holding its sorted share."""
@@ -163,6 +270,7 @@ class DistributedRadixSort:
         self._recv = None
         self._xcap = 0
         self.fused = hasattr(local_ops, "scatter_exchange")
+        self.exchange = hasattr(local_ops, "begin")  # CudaExchangeOps: the whole sort is C++ (thrs_xchg_*)
 
     def _recv_buffers(self, like_k, like_v, count):
         import torch
@@ -184,6 +292,9 @@ class DistributedRadixSort:
         def mark(name):
             if timers is not None:
                 timers.mark(name)
+
+        if self.exchange:
+            return self._exchange_sort(keys, vals, n, mark)
 
         # 1-2: top-digit histogram of the slice, shared with everyone
         hist = ops.top_digit_histogram(keys, n)
@@ -215,6 +326,36 @@ class DistributedRadixSort:
         mark("local sort")
         return rk, rv, total_recv
 
+
+    def reserve(self, max_local, capacity=None):
+        """COLLECTIVE (exchange path): size the per-rank buffers for slices of up to max_local items and
+        shares of up to `capacity` items (default: 6 % above max_local) — same numbers on every rank."""
+        capacity = int(max_local * 1.06) + 4096 if capacity is None else int(capacity)
+        self.ops.reserve(self.dist, self.group, int(max_local), capacity)
+
+    def _exchange_sort(self, keys, vals, n, mark):
+        import torch
+
+        ops = self.ops
+        if ops._x is None or n > ops.max_local:
+            # first use (or a larger slice): agree on the sizes once; later sorts involve no collective
+            sizes = [None] * self.world
+            self.dist.all_gather_object(sizes, n, group=self.group)
+            self.reserve(max(sizes))
+        stream = torch.cuda.current_stream().cuda_stream
+        for attempt in range(2):
+            ops.begin(keys, vals, n, stream)
+            mark("top-digit histogram + partition pass (sort pass 4 of 4)")
+            kptr, vptr, cnt, need, ok = ops.finish(stream)
+            if ok:
+                mark("bucket exchange (copy engines) overlapped with the segmented 3-pass sort")
+                rk, rv = ops.views(kptr, vptr, cnt, keys.dtype, vals.dtype)
+                return rk, rv, cnt
+            # skewed keys: a share did not fit.  Every rank saw the same table and failed alike, before anything
+            # was copied: rebuild with the exact need (collective) and run the sort again
+            torch.cuda.synchronize()
+            self.reserve(ops.max_local, int(need * 1.02) + 4096)
+        raise RuntimeError("exchange capacity could not be sized")
 
     def _fused_exchange_and_sort(self, keys, vals, n, bits, all_h, dest, send, total_recv, mark):
         import torch
@@ -303,20 +444,28 @@ def verify_distributed(torch, dist, g, rk, rv, count, total):
 
 
 def bench(args, dist, rank, world, dev, g):
-    """bench.py at N > 1: the partitioned sort, `--log2n-per-gpu` pairs per GPU (weak scaling)."""
+    """bench.py at N > 1: the partitioned sort.  Weak scaling by default (`--log2n-per-gpu` pairs per
+    GPU); `--log2n-total T` fixes the total instead (strong scaling; T = 32 is config C5)."""
     import json
+    import os
     import time
 
     import torch
 
-    n_l = 1 << args.log2n_per_gpu
+    from . import RadixSort
+
+    strong = bool(getattr(args, "log2n_total", 0))
+    n_l = (1 << args.log2n_total) // world if strong else 1 << args.log2n_per_gpu
     total = n_l * world
+    mode = os.environ.get("THRS_MG_MODE", "exchange")  # "scatter" = round 1's fused partition+exchange kernel (A/B)
     keys0, vals0 = g["gen_pairs"](torch, rank * n_l, n_l, dev)
-    ops = CudaLocalOps("u32", 4)
-    ops.reserve(int(n_l * 1.05) + 4096)
+    if mode == "scatter":
+        ops = CudaLocalOps("u32", 4)
+        ops.reserve(int(n_l * 1.05) + 4096)
+    else:
+        ops = CudaExchangeOps("u32", 4, groups=int(os.environ.get("THRS_MG_GROUPS", "4")))
     ds = DistributedRadixSort(dist, ops, "u32")
     keys, vals = torch.empty_like(keys0), torch.empty_like(vals0)
-    stream = torch.cuda.current_stream()
 
     def step():
         keys.copy_(keys0)
@@ -344,72 +493,126 @@ def bench(args, dist, rank, world, dev, g):
     torch.cuda.synchronize()
     clocks = sampler.stop()
     verified = verify_distributed(torch, dist, g, rk, rv, cnt, total)
+    xstats = ops.stats() if mode != "scatter" else {}
     total_ms = sum(step_ms)
     value = total * args.steps / (total_ms * 1e-3)
 
-    # per-pass device time of the local sort (dominant kernel), measured live with the sorter's events
-    ops.sorter.profile(True)
-    keys.copy_(keys0)
-    vals.copy_(vals0)
-    ds.sort_pairs(keys, vals)
-    prof = ops.sorter.readProfile()
-    ops.sorter.profile(False)
-    launches_per_step = 1 + 1 + 6  # top-digit histogram, scatter pass, local sort (zero + histogram + 4)
+    # What bounds the step.  (1) per-pass device time of the dominant kernel, measured live with the sorter's
+    # events on a plain local sort of this rank's slice; (2) the segmented 3-pass sort of what this rank
+    # received, alone (nothing in flight): finish-stage time minus this = the part of the exchange NOT hidden.
+    stream = torch.cuda.current_stream()
+    srt = RadixSort([], RadixSort.Config().configureWithKeyPair("u32", 4))
+    tmp = torch.empty(srt.getTemporaryBufferBytes(n_l).getTemporaryBufferBytesForSortPairs(), dtype=torch.uint8, device=dev)
+    srt.profile(True)
+    for _ in range(2):
+        keys.copy_(keys0)
+        vals.copy_(vals0)
+        srt.sortPairs(keys, vals, n_l, tmp, 0, 32, stream)
+        prof = srt.readProfile()
+    srt.profile(False)
+    seg_alone_ms = None
+    if mode != "scatter" and cnt:
+        del tmp
+        k = (rk.to(torch.int64) & 0xFFFFFFFF) >> 24
+        lo, hi = int(k[0]), int(k[-1])
+        edges = torch.searchsorted(k, torch.arange(lo, hi + 2, device=dev, dtype=torch.int64)).tolist()
+        del k
+        sk, sv = rk.clone(), rv.clone()
+        stmp = torch.empty(srt.getSegmentsTemporaryBufferBytes(cnt, len(edges) - 1, True), dtype=torch.uint8, device=dev)
+        best = None
+        for _ in range(3):  # already sorted input: the passes move the same bytes, ranking cost is that of 1-digit warps on pass 3 only
+            sk.copy_(keys0[:cnt] if cnt <= n_l else rk)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            srt.sortSegments(sk, sv, edges, stmp, 0, 24, stream)
+            b.record(stream)
+            b.synchronize()
+            best = a.elapsed_time(b) if best is None else min(best, a.elapsed_time(b))
+        seg_alone_ms = best
+        del sk, sv, stmp
+    torch.cuda.empty_cache()
 
     # end to end: pinned host slices in, sorted share out (H2D + sort + D2H inside the timed region)
-    hk0, hv0 = keys0.cpu().pin_memory(), vals0.cpu().pin_memory()
-    hk_out = torch.empty(int(n_l * 1.05) + 4096, dtype=hk0.dtype).pin_memory()
-    hv_out = torch.empty_like(hk_out).pin_memory()
-    e2e = []
-    for i in range(1 + max(1, min(args.steps, args.e2e_steps))):
-        torch.cuda.synchronize()
-        dist.barrier()
-        t0 = time.perf_counter()
-        keys.copy_(hk0, non_blocking=True)
-        vals.copy_(hv0, non_blocking=True)
-        rk, rv, cnt = ds.sort_pairs(keys, vals)
-        hk_out[:cnt].copy_(rk[:cnt], non_blocking=True)
-        hv_out[:cnt].copy_(rv[:cnt], non_blocking=True)
-        torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        if i > 0:
-            e2e.append(float(dt.item()))
-    e2e_value = total * len(e2e) / sum(e2e)
+    e2e_value, e2e_ms, e2e_note = None, None, None
+    if n_l <= (1 << 29):
+        hk0, hv0 = keys0.cpu().pin_memory(), vals0.cpu().pin_memory()
+        hk_out = torch.empty(int(n_l * 1.06) + 8192, dtype=hk0.dtype).pin_memory()
+        hv_out = torch.empty_like(hk_out).pin_memory()
+        e2e = []
+        for i in range(1 + max(1, min(args.steps, args.e2e_steps))):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            keys.copy_(hk0, non_blocking=True)
+            vals.copy_(hv0, non_blocking=True)
+            rk, rv, cnt = ds.sort_pairs(keys, vals)
+            hk_out[:cnt].copy_(rk[:cnt], non_blocking=True)
+            hv_out[:cnt].copy_(rv[:cnt], non_blocking=True)
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            if i > 0:
+                e2e.append(float(dt.item()))
+        e2e_value, e2e_ms = total * len(e2e) / sum(e2e), 1e3 * sum(e2e) / len(e2e)
+    else:
+        e2e_note = "skipped: pinned host copies of >= 2^30 pairs per rank (32+ GiB of pinned memory per process)"
 
     if rank == 0:
         peak, peak_src = g["_peaks"]()
-        per_gpu_bytes = 2.0 * cnt * 8
+        per_gpu_bytes = 2.0 * n_l * 8
         avg_pass = sum(prof["pass_ms"]) / len(prof["pass_ms"])
         achieved = per_gpu_bytes / (avg_pass * 1e-3) / 1e9
-        send_bytes = n_l * 8 * (world - 1) / world
-        fused = "partition+exchange (peer stores)" in stage_sum
-        a2a_ms = stage_sum.get("partition+exchange (peer stores)" if fused else "all-to-all", 0.0) / args.steps
+        stage_ms = {k: v / args.steps for k, v in stage_sum.items()}
+        if mode == "scatter":
+            send_bytes = n_l * 8 * (world - 1) / world
+            x_ms = stage_ms.get("partition+exchange (peer stores)", 0.0)
+            exchange = {"how": "round-1 path: partition pass storing into peer memory (P2P stores, CUDA IPC)",
+                        "bytes_sent_per_gpu": send_bytes, "ms": x_ms,
+                        "GBps_per_direction_per_gpu": (send_bytes / (x_ms * 1e-3) / 1e9) if x_ms else None, "nvlink_peak_GBps": 900.0}
+            launches_per_step = 1 + 1 + 6
+            how = "MSD splitters + partition pass storing into peer memory over NVLink + local 4-pass onesweep"
+        else:
+            fin = [v for k, v in stage_ms.items() if k.startswith("bucket exchange")][0]
+            send_bytes = xstats["sent_remote_bytes"]
+            exposed = None if seg_alone_ms is None else max(fin - seg_alone_ms, 0.0)
+            exchange = {"how": "copy-engine copies of (digit, source) chunks into the owners' windows (CUDA IPC), digit-major / source-minor, "
+                               f"{ops.groups} groups per rank, 4-byte flag per group, cuStreamWaitValue32 on the owner's stream",
+                        "bytes_sent_per_gpu_rank0": send_bytes, "bucket_copies_per_step_rank0": xstats["bucket_copies"],
+                        "finish_stage_ms": fin, "segmented_sort_alone_ms": seg_alone_ms,
+                        "exchange_not_hidden_ms": exposed,
+                        "overlap_fraction_of_copy_time": None if exposed is None or not send_bytes else
+                        max(0.0, 1.0 - exposed / (send_bytes / 750e9 * 1e3)),
+                        "GBps_per_direction_per_gpu_lower_bound": send_bytes / (fin * 1e-3) / 1e9 if fin else None,
+                        "nvlink_peak_GBps": 900.0,
+                        "limiter": "segmented sort (SM shared-memory pipe)" if exposed is not None and exposed < 0.25 * fin else "NVLink copies"}
+            launches_per_step = xstats["kernel_launches"]
+            how = ("top-digit histogram + ONE stable top-digit pass (the sort's pass 4) + copy-engine bucket exchange over NVLink "
+                   "overlapped with a segmented 3-pass onesweep on bits [0,24) of the received buckets")
         line = {
             "metric": g["METRIC"], "value": value, "unit": g["UNIT"], "n_gpus": world, "steps": args.steps,
-            "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "strong" if strong else "weak",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": f"C5 shape: {world} x 2^{args.log2n_per_gpu} uniform-random u32 key + u32 value pairs, "
-                                   "MSD splitters + partition pass storing into peer memory over NVLink + local onesweep, stable, bits [0,32)",
-                       "n_total": total, "n_per_gpu": n_l, "parallelism": f"partitioned sort over {world} ranks (NCCL)",
+            "config": {"workload": f"C5{'' if strong and args.log2n_total == 32 else ' shape'}: {world} x {n_l} uniform-random u32 key + u32 value pairs "
+                                   f"(2^{total.bit_length() - 1} total), {how}, stable, bits [0,32)",
+                       "n_total": total, "n_per_gpu": n_l,
+                       "parallelism": f"partitioned sort over {world} ranks, one process per GPU (torch.distributed/NCCL only passes IPC handles and the timing all_reduce)",
                        "l2": "per-GPU inputs (>= 2 GiB) are larger than L2; input restored outside the timed events",
-                       "stage_ms_rank0": {k: v / args.steps for k, v in stage_sum.items()},
-                       "all_to_all": {"how": "fused into the partition kernel (P2P stores, CUDA IPC)" if fused else "NCCL all_to_all_single",
-                                      "bytes_sent_per_gpu": send_bytes, "ms": a2a_ms,
-                                      "GBps_per_direction_per_gpu": (send_bytes / (a2a_ms * 1e-3) / 1e9) if a2a_ms else None,
-                                      "nvlink_peak_GBps": 900.0}},
+                       "stage_ms_rank0": stage_ms, "exchange": exchange, "mode": mode},
             "verified": verified,
-            "roofline": {"bound": "hbm", "kernel": "onesweep_kernel (one 8-bit pass of the local sort, rank 0)",
+            "roofline": {"bound": "hbm", "kernel": "onesweep_kernel (one 8-bit pass over this rank's slice, rank 0)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": g["_traffic"](), "peak_source": peak_src, "bytes_per_launch": per_gpu_bytes,
                          "avg_launch_ms": avg_pass},
             "e2e": {"value": e2e_value, "unit": g["UNIT"], "h2d_bytes_per_step": total * 8, "d2h_bytes_per_step": total * 8,
-                    "ms_per_step": 1e3 * sum(e2e) / len(e2e), "api": "DistributedRadixSort.sort_pairs (pinned host slices)"},
+                    "ms_per_step": e2e_ms, "api": "DistributedRadixSort.sort_pairs (pinned host slices)", "note": e2e_note},
             "gpu_launches": launches_per_step * args.steps * world,
             "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
+    if hasattr(ops, "close"):
+        ops.close()
     dist.destroy_process_group()
     return 0 if verified else 1
 
