@@ -108,6 +108,10 @@ struct thrs_xchg {
     // what the last finish computed (introspection for benchmarks and tests)
     uint64_t last_recv = 0, last_sent_remote_bytes = 0;
     uint32_t last_launches = 0, last_copies = 0;
+    // plan of the sort in flight (thrs_xchg_send -> thrs_xchg_recv)
+    int32_t owner[256] = {}, group[256] = {};
+    uint64_t tot[256] = {}, recv[MAX_WORLD] = {};
+    int phase = 0; // 0 idle, 1 begun, 2 sent
 
     uint32_t* flag_ptr(char* win, int parity, int src, int slot) const
     {
@@ -321,44 +325,53 @@ int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t
         X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, x->rank, MAX_GROUPS), x->d_epoch + par, 4, cudaMemcpyDefault, x->side),
                "push counts flag");
     }
-    int rc = wait_flags(x, x->side, par, MAX_GROUPS);
-    if (rc) return rc;
-    for (int s = 0; s < x->world; ++s)
-        X_CUDA(cudaMemcpyAsync(x->h_counts + (size_t)s * 256, x->counts_ptr(x->window, par, s), 1024, cudaMemcpyDeviceToHost, x->side),
-               "read counts");
-    X_CUDA(cudaEventRecord(x->ev_host, x->side), "cudaEventRecord");
+    // (the wait for everyone's counts is enqueued by thrs_xchg_send: a context never enqueues a wait before
+    // everything other ranks need from it for the same step has been enqueued — see the note at thrs_xchg_send)
     x->began = true;
+    x->phase = 1;
     return THRS_OK;
 }
 
-int thrs_xchg_finish(thrs_xchg* x, void* stream_, void** out_keys, void** out_values, uint64_t* out_count,
-                     uint64_t* needed_capacity)
+// Ordering rule that keeps the exchange free of deadlocks even where streams share a hardware queue (a
+// blocked cuStreamWaitValue32 stalls every stream behind it in the same queue): a context enqueues a WAIT
+// only after it has enqueued everything other ranks need from it for that step.  begin enqueues the counts
+// push; send enqueues the wait for the gathered counts (all pushes are out), then all bucket copies; recv
+// enqueues the waits for the groups (all copies are out).  One process per GPU: begin, send, recv in a
+// row.  One process driving several ranks (thrs_mg_*): begin for all, send for all, recv for all.
+int thrs_xchg_send(thrs_xchg* x, void* stream_, uint64_t* needed_capacity)
 {
-    if (!x || !out_keys || !out_values || !out_count) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_finish: NULL argument");
-    if (!x->began) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_finish: thrs_xchg_begin first");
-    x->began = false;
+    if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send: NULL context");
+    if (x->phase != 1) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send: thrs_xchg_begin first");
+    x->phase = 0;
     DeviceGuard g(x->device);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank;
+    // everyone's counts -> host
+    int rc = wait_flags(x, x->side, par, MAX_GROUPS);
+    if (rc) return rc;
+    for (int s = 0; s < P; ++s)
+        X_CUDA(cudaMemcpyAsync(x->h_counts + (size_t)s * 256, x->counts_ptr(x->window, par, s), 1024, cudaMemcpyDeviceToHost, x->side),
+               "read counts");
+    X_CUDA(cudaEventRecord(x->ev_host, x->side), "cudaEventRecord");
     X_CUDA(cudaEventSynchronize(x->ev_host), "waiting for the gathered histograms");
 
     std::vector<uint64_t> counts((size_t)P * 256);
     for (size_t i = 0; i < counts.size(); ++i) counts[i] = x->h_counts[i];
-    int32_t owner[256], group[256];
-    uint64_t recv[MAX_WORLD];
-    thrs_xchg_plan(P, x->groups, counts.data(), owner, recv, group);
+    thrs_xchg_plan(P, x->groups, counts.data(), x->owner, x->recv, x->group);
+    const int32_t* owner = x->owner;
+    const int32_t* group = x->group;
     uint64_t need = 0;
-    for (int r = 0; r < P; ++r) need = recv[r] > need ? recv[r] : need;
+    for (int r = 0; r < P; ++r) need = x->recv[r] > need ? x->recv[r] : need;
     if (needed_capacity) *needed_capacity = need;
     if (need > x->capacity) {
-        // every rank sees the same table and takes the same decision: nobody has copied anything yet
+        // every rank sees the same table and takes the same decision: nobody copies anything
         X_CUDA(cudaStreamWaitEvent(stream, x->ev_part, 0), "cudaStreamWaitEvent");
-        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_finish: a rank's share exceeds the receive capacity (see needed_capacity)");
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send: a rank's share exceeds the receive capacity (see needed_capacity)");
     }
 
     // where my bucket d starts in my send buffers, and where my chunk of bucket d lands at its owner:
     // digit-major / source-minor inside the owner's receive buffer
-    uint64_t send_base[257], land[256], tot[256];
+    uint64_t send_base[257], land[256];
     send_base[0] = 0;
     for (int d = 0; d < 256; ++d) send_base[d + 1] = send_base[d] + counts[(size_t)me * 256 + d];
     {
@@ -372,7 +385,7 @@ int thrs_xchg_finish(thrs_xchg* x, void* stream_, void** out_keys, void** out_va
                 t += counts[(size_t)s * 256 + d];
             }
             land[d] = mine;
-            tot[d] = t;
+            x->tot[d] = t;
             run += t;
         }
     }
@@ -398,22 +411,34 @@ int thrs_xchg_finish(thrs_xchg* x, void* stream_, void** out_keys, void** out_va
         }
     }
     for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
+    x->last_sent_remote_bytes = remote_bytes;
+    x->phase = 2;
+    return THRS_OK;
+}
 
+int thrs_xchg_recv(thrs_xchg* x, void* stream_, void** out_keys, void** out_values, uint64_t* out_count)
+{
+    if (!x || !out_keys || !out_values || !out_count) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_recv: NULL argument");
+    if (x->phase != 2) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_recv: thrs_xchg_send first");
+    x->phase = 0;
+    x->began = false;
+    DeviceGuard g(x->device);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank;
     // ---- incoming: as soon as a group is complete, sort its buckets on the remaining low bits
     int in_alt = 0;
-    bool any = false;
     for (int gi = 0; gi < x->groups; ++gi) {
         uint64_t seg_begin[257];
         uint32_t nseg = 0;
         uint64_t run = 0;
         bool started = false;
         for (int d = 0; d < 256; ++d) {
-            if (owner[d] != me) continue;
-            if (group[d] == gi) {
+            if (x->owner[d] != me) continue;
+            if (x->group[d] == gi) {
                 if (!started) { seg_begin[0] = run; started = true; }
-                seg_begin[++nseg] = run + tot[d];
+                seg_begin[++nseg] = run + x->tot[d];
             }
-            run += tot[d];
+            run += x->tot[d];
         }
         int rc = wait_flags(x, stream, par, gi);
         if (rc) return rc;
@@ -423,17 +448,22 @@ int thrs_xchg_finish(thrs_xchg* x, void* stream_, void** out_keys, void** out_va
                                      x->seg_scratch, x->seg_scratch_bytes, seg_begin, nseg, 0, x->key_bits - 8, stream, &ia));
         x->last_launches += (uint32_t)thrs_last_launch_count();
         in_alt = ia;
-        any = true;
     }
     // the send buffers may be overwritten by the next sort only after my own copies have left
     for (int r = 0; r < P; ++r) X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
-    (void)any;
     *out_keys = in_alt ? x->alt_keys : x->window + x->off_keys;
     *out_values = in_alt ? x->alt_vals : x->window + x->off_vals;
-    *out_count = recv[me];
-    x->last_recv = recv[me];
-    x->last_sent_remote_bytes = remote_bytes;
+    *out_count = x->recv[me];
+    x->last_recv = x->recv[me];
     return THRS_OK;
+}
+
+int thrs_xchg_finish(thrs_xchg* x, void* stream, void** out_keys, void** out_values, uint64_t* out_count,
+                     uint64_t* needed_capacity)
+{
+    int rc = thrs_xchg_send(x, stream, needed_capacity);
+    if (rc) return rc;
+    return thrs_xchg_recv(x, stream, out_keys, out_values, out_count);
 }
 
 int thrs_xchg_stats(thrs_xchg* x, uint64_t* received_items, uint64_t* sent_remote_bytes, uint32_t* kernel_launches,
