@@ -242,12 +242,16 @@ THRS_API int thrs_xchg_set_peers(thrs_xchg* x, void* const* window_bases);
 THRS_API int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t n, void* stream);
 THRS_API int thrs_xchg_finish(thrs_xchg* x, void* stream, void** out_keys, void** out_values, uint64_t* out_count,
                               uint64_t* needed_capacity);
-/* finish = send + recv.  A host that drives SEVERAL ranks from one thread must call begin for all of
- * them, then send for all, then recv for all: a context only ever enqueues a wait after everything the
- * other ranks need from it has been enqueued, which keeps the exchange deadlock-free even where streams
- * share a hardware queue (a blocked cuStreamWaitValue32 stalls the whole queue). */
-THRS_API int thrs_xchg_send(thrs_xchg* x, void* stream, uint64_t* needed_capacity);
-THRS_API int thrs_xchg_recv(thrs_xchg* x, void* stream, void** out_keys, void** out_values, uint64_t* out_count);
+/* finish = plan_step, then send_group / recv_group alternating over the groups, then result.  A host
+ * that drives SEVERAL ranks from one thread must run every step for ALL ranks before the next one
+ * (begin for all; plan_step for all; per group: send_group for all, recv_group for all; result for
+ * all): a context enqueues the wait of a step only after everything the other ranks need from it for
+ * that step is enqueued, which keeps the exchange deadlock-free even where streams share a hardware
+ * queue (a blocked cuStreamWaitValue32 stalls the whole queue). */
+THRS_API int thrs_xchg_plan_step(thrs_xchg* x, void* stream, uint64_t* needed_capacity, int* groups);
+THRS_API int thrs_xchg_send_group(thrs_xchg* x);
+THRS_API int thrs_xchg_recv_group(thrs_xchg* x, void* stream);
+THRS_API int thrs_xchg_result(thrs_xchg* x, void* stream, void** out_keys, void** out_values, uint64_t* out_count);
 /* Of the last begin/finish pair: items received, bytes sent to OTHER ranks, kernels launched, bucket copies enqueued. */
 THRS_API int thrs_xchg_stats(thrs_xchg* x, uint64_t* received_items, uint64_t* sent_remote_bytes, uint32_t* kernel_launches,
                              uint32_t* bucket_copies);

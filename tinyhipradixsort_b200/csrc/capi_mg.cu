@@ -151,18 +151,30 @@ int thrs_mg_sort_pairs(thrs_mg* m, const void* const* keys, const void* const* v
         std::vector<void*> rk(ndev), rv(ndev);
         uint64_t need = 0;
         int rc = THRS_OK;
-        // all sends before any receive: a rank's waits are enqueued only after every rank's copies are
-        // (the streams of all ranks share this process's hardware queues; see thrs_xchg_send)
+        // every step for ALL ranks before the next step: a rank's wait is enqueued only after every rank has
+        // enqueued what that wait depends on (all ranks' streams share this process's hardware queues)
+        int groups = 0;
         for (int g = 0; g < ndev; ++g) {
             MG_CUDA(cudaSetDevice(m->dev[g].id), "cudaSetDevice");
             uint64_t nd = 0;
-            const int r = thrs_xchg_send(m->dev[g].x, m->dev[g].stream, &nd);
+            const int r = thrs_xchg_plan_step(m->dev[g].x, m->dev[g].stream, &nd, &groups);
             need = nd > need ? nd : need;
             if (r != THRS_OK && rc == THRS_OK) { rc = r; snprintf(g_mg_err, sizeof(g_mg_err), "%s", thrs_xchg_last_error()); }
         }
+        for (int gi = 0; gi < groups && rc == THRS_OK; ++gi) {
+            for (int g = 0; g < ndev && rc == THRS_OK; ++g) {
+                MG_CUDA(cudaSetDevice(m->dev[g].id), "cudaSetDevice");
+                rc = thrs_xchg_send_group(m->dev[g].x);
+            }
+            for (int g = 0; g < ndev && rc == THRS_OK; ++g) {
+                MG_CUDA(cudaSetDevice(m->dev[g].id), "cudaSetDevice");
+                rc = thrs_xchg_recv_group(m->dev[g].x, m->dev[g].stream);
+            }
+            if (rc != THRS_OK) snprintf(g_mg_err, sizeof(g_mg_err), "%s", thrs_xchg_last_error());
+        }
         for (int g = 0; g < ndev && rc == THRS_OK; ++g) {
             MG_CUDA(cudaSetDevice(m->dev[g].id), "cudaSetDevice");
-            rc = thrs_xchg_recv(m->dev[g].x, m->dev[g].stream, &rk[g], &rv[g], &out_counts[g]);
+            rc = thrs_xchg_result(m->dev[g].x, m->dev[g].stream, &rk[g], &rv[g], &out_counts[g]);
             if (rc != THRS_OK) snprintf(g_mg_err, sizeof(g_mg_err), "%s", thrs_xchg_last_error());
         }
         if (rc != THRS_OK) {

@@ -100,18 +100,21 @@ struct thrs_xchg {
     uint32_t* h_epoch = nullptr;  // pinned [2]
     uint32_t* h_counts = nullptr; // pinned [world][256]
     cudaStream_t side = nullptr;
-    cudaStream_t copy[MAX_WORLD] = {};
-    cudaEvent_t ev_counts = nullptr, ev_part = nullptr, ev_host = nullptr, ev_copy[MAX_WORLD] = {};
+    cudaStream_t copy[MAX_WORLD] = {};  // keys (and the group flags) to rank r
+    cudaStream_t copyv[MAX_WORLD] = {}; // values to rank r, so that two copy engines work per destination
+    cudaEvent_t ev_counts = nullptr, ev_part = nullptr, ev_host = nullptr, ev_copy[MAX_WORLD] = {}, ev_copyv[MAX_WORLD] = {};
     uint32_t epoch = 0;
     uint64_t n_local = 0;
     bool began = false;
     // what the last finish computed (introspection for benchmarks and tests)
     uint64_t last_recv = 0, last_sent_remote_bytes = 0;
     uint32_t last_launches = 0, last_copies = 0;
-    // plan of the sort in flight (thrs_xchg_send -> thrs_xchg_recv)
+    // plan of the sort in flight (thrs_xchg_plan_step -> send_group / recv_group -> result)
     int32_t owner[256] = {}, group[256] = {};
     uint64_t tot[256] = {}, recv[MAX_WORLD] = {};
-    int phase = 0; // 0 idle, 1 begun, 2 sent
+    int phase = 0; // 0 idle, 1 begun, 2 planned (groups are being sent / received)
+    uint64_t send_base[257] = {}, land[256] = {}, my_counts[256] = {};
+    int sent_groups = 0, recv_groups = 0, in_alt = 0;
 
     uint32_t* flag_ptr(char* win, int parity, int src, int slot) const
     {
@@ -207,7 +210,9 @@ void thrs_xchg_destroy(thrs_xchg* x)
     if (x->side) cudaStreamDestroy(x->side);
     for (int r = 0; r < MAX_WORLD; ++r) {
         if (x->copy[r]) cudaStreamDestroy(x->copy[r]);
+        if (x->copyv[r]) cudaStreamDestroy(x->copyv[r]);
         if (x->ev_copy[r]) cudaEventDestroy(x->ev_copy[r]);
+        if (x->ev_copyv[r]) cudaEventDestroy(x->ev_copyv[r]);
     }
     for (cudaEvent_t e : {x->ev_counts, x->ev_part, x->ev_host})
         if (e) cudaEventDestroy(e);
@@ -266,7 +271,9 @@ int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_l
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->side, cudaStreamNonBlocking);
         for (int r = 0; r < world && e == cudaSuccess; ++r) {
             e = cudaStreamCreateWithFlags(&x->copy[r], cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->copyv[r], cudaStreamNonBlocking);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_copy[r], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_copyv[r], cudaEventDisableTiming);
         }
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_counts, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_part, cudaEventDisableTiming);
@@ -325,23 +332,25 @@ int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t
         X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, x->rank, MAX_GROUPS), x->d_epoch + par, 4, cudaMemcpyDefault, x->side),
                "push counts flag");
     }
-    // (the wait for everyone's counts is enqueued by thrs_xchg_send: a context never enqueues a wait before
-    // everything other ranks need from it for the same step has been enqueued — see the note at thrs_xchg_send)
+    // (the wait for everyone's counts is enqueued by thrs_xchg_plan_step: a context never enqueues a wait before
+    // everything other ranks need from it for the same step has been enqueued — see the note there)
     x->began = true;
     x->phase = 1;
     return THRS_OK;
 }
 
 // Ordering rule that keeps the exchange free of deadlocks even where streams share a hardware queue (a
-// blocked cuStreamWaitValue32 stalls every stream behind it in the same queue): a context enqueues a WAIT
-// only after it has enqueued everything other ranks need from it for that step.  begin enqueues the counts
-// push; send enqueues the wait for the gathered counts (all pushes are out), then all bucket copies; recv
-// enqueues the waits for the groups (all copies are out).  One process per GPU: begin, send, recv in a
-// row.  One process driving several ranks (thrs_mg_*): begin for all, send for all, recv for all.
-int thrs_xchg_send(thrs_xchg* x, void* stream_, uint64_t* needed_capacity)
+// blocked cuStreamWaitValue32 stalls every stream behind it in the same queue): a context enqueues the WAIT
+// for a step only after it has enqueued everything other ranks need from it for that step.  begin enqueues
+// the counts push; plan enqueues the wait for the gathered counts (all pushes are out); send_group(g)
+// enqueues group g's bucket copies; recv_group(g) the wait for group g's flags (group g's copies are out)
+// and the segmented sort of group g.  By induction over the steps every wait is eventually satisfied.
+// One process per GPU: begin, plan, then send_group / recv_group alternating (thrs_xchg_finish).  One
+// process driving several ranks (thrs_mg_*): each step for ALL ranks before the next step.
+int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, int* groups)
 {
-    if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send: NULL context");
-    if (x->phase != 1) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send: thrs_xchg_begin first");
+    if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_plan_step: NULL context");
+    if (x->phase != 1) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_plan_step: thrs_xchg_begin first");
     x->phase = 0;
     DeviceGuard g(x->device);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -358,112 +367,138 @@ int thrs_xchg_send(thrs_xchg* x, void* stream_, uint64_t* needed_capacity)
     std::vector<uint64_t> counts((size_t)P * 256);
     for (size_t i = 0; i < counts.size(); ++i) counts[i] = x->h_counts[i];
     thrs_xchg_plan(P, x->groups, counts.data(), x->owner, x->recv, x->group);
-    const int32_t* owner = x->owner;
-    const int32_t* group = x->group;
     uint64_t need = 0;
     for (int r = 0; r < P; ++r) need = x->recv[r] > need ? x->recv[r] : need;
     if (needed_capacity) *needed_capacity = need;
+    if (groups) *groups = x->groups;
     if (need > x->capacity) {
         // every rank sees the same table and takes the same decision: nobody copies anything
         X_CUDA(cudaStreamWaitEvent(stream, x->ev_part, 0), "cudaStreamWaitEvent");
-        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send: a rank's share exceeds the receive capacity (see needed_capacity)");
+        return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg: a rank's share exceeds the receive capacity (see needed_capacity)");
     }
-
     // where my bucket d starts in my send buffers, and where my chunk of bucket d lands at its owner:
     // digit-major / source-minor inside the owner's receive buffer
-    uint64_t send_base[257], land[256];
-    send_base[0] = 0;
-    for (int d = 0; d < 256; ++d) send_base[d + 1] = send_base[d] + counts[(size_t)me * 256 + d];
-    {
-        uint64_t run = 0;
-        int cur = -1;
-        for (int d = 0; d < 256; ++d) {
-            if (owner[d] != cur) { cur = owner[d]; run = 0; }
-            uint64_t t = 0, mine = 0;
-            for (int s = 0; s < P; ++s) {
-                if (s == me) mine = run + t;
-                t += counts[(size_t)s * 256 + d];
-            }
-            land[d] = mine;
-            x->tot[d] = t;
-            run += t;
-        }
+    x->send_base[0] = 0;
+    for (int d = 0; d < 256; ++d) {
+        x->my_counts[d] = counts[(size_t)me * 256 + d];
+        x->send_base[d + 1] = x->send_base[d] + x->my_counts[d];
     }
-
-    // ---- outgoing: group by group, one copy stream per destination, a flag after every group
-    uint64_t remote_bytes = 0;
-    for (int r = 0; r < P; ++r) X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_part, 0), "cudaStreamWaitEvent");
-    for (int gi = 0; gi < x->groups; ++gi) {
-        for (int i = 1; i <= P; ++i) {
-            const int r = (me + i) % P; // the own rank last: local copies are the cheapest to delay
-            for (int d = 0; d < 256; ++d) {
-                if (owner[d] != r || group[d] != gi) continue;
-                const uint64_t c = counts[(size_t)me * 256 + d];
-                if (!c) continue;
-                X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + land[d] * x->kbytes, x->send_keys + send_base[d] * x->kbytes,
-                                       c * x->kbytes, cudaMemcpyDefault, x->copy[r]), "bucket copy (keys)");
-                X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_vals + land[d] * x->vbytes, x->send_vals + send_base[d] * x->vbytes,
-                                       c * x->vbytes, cudaMemcpyDefault, x->copy[r]), "bucket copy (values)");
-                if (r != me) remote_bytes += c * (uint64_t)(x->kbytes + x->vbytes);
-                x->last_copies += 2;
-            }
-            X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDefault, x->copy[r]), "group flag");
+    uint64_t run = 0;
+    int cur = -1;
+    for (int d = 0; d < 256; ++d) {
+        if (x->owner[d] != cur) { cur = x->owner[d]; run = 0; }
+        uint64_t t = 0, mine = 0;
+        for (int s = 0; s < P; ++s) {
+            if (s == me) mine = run + t;
+            t += counts[(size_t)s * 256 + d];
         }
+        x->land[d] = mine;
+        x->tot[d] = t;
+        run += t;
     }
-    for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
-    x->last_sent_remote_bytes = remote_bytes;
+    for (int r = 0; r < P; ++r) {
+        X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_part, 0), "cudaStreamWaitEvent");
+        X_CUDA(cudaStreamWaitEvent(x->copyv[r], x->ev_part, 0), "cudaStreamWaitEvent");
+    }
+    x->last_sent_remote_bytes = 0;
+    x->sent_groups = x->recv_groups = 0;
+    x->in_alt = 0;
     x->phase = 2;
     return THRS_OK;
 }
 
-int thrs_xchg_recv(thrs_xchg* x, void* stream_, void** out_keys, void** out_values, uint64_t* out_count)
+// outgoing buckets of the next group: keys and values on two streams per destination, then the group's flag
+int thrs_xchg_send_group(thrs_xchg* x)
 {
-    if (!x || !out_keys || !out_values || !out_count) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_recv: NULL argument");
-    if (x->phase != 2) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_recv: thrs_xchg_send first");
+    if (!x || x->phase != 2 || x->sent_groups >= x->groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send_group: out of sequence");
+    DeviceGuard g(x->device);
+    const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank, gi = x->sent_groups;
+    for (int i = 1; i <= P; ++i) {
+        const int r = (me + i) % P; // the own rank last: local copies are the cheapest to delay
+        bool any = false;
+        for (int d = 0; d < 256; ++d) {
+            if (x->owner[d] != r || x->group[d] != gi) continue;
+            const uint64_t c = x->my_counts[d];
+            if (!c) continue;
+            X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + x->land[d] * x->kbytes, x->send_keys + x->send_base[d] * x->kbytes,
+                                   c * x->kbytes, cudaMemcpyDefault, x->copy[r]), "bucket copy (keys)");
+            X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_vals + x->land[d] * x->vbytes, x->send_vals + x->send_base[d] * x->vbytes,
+                                   c * x->vbytes, cudaMemcpyDefault, x->copyv[r]), "bucket copy (values)");
+            if (r != me) x->last_sent_remote_bytes += c * (uint64_t)(x->kbytes + x->vbytes);
+            x->last_copies += 2;
+            any = true;
+        }
+        if (any) { // the flag follows BOTH streams
+            X_CUDA(cudaEventRecord(x->ev_copyv[r], x->copyv[r]), "cudaEventRecord");
+            X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_copyv[r], 0), "cudaStreamWaitEvent");
+        }
+        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDefault, x->copy[r]), "group flag");
+    }
+    ++x->sent_groups;
+    if (x->sent_groups == x->groups)
+        for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
+    return THRS_OK;
+}
+
+// incoming buckets of the next group: wait for its flags on `stream`, then sort its buckets on the low bits
+int thrs_xchg_recv_group(thrs_xchg* x, void* stream_)
+{
+    if (!x || x->phase != 2 || x->recv_groups >= x->sent_groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_recv_group: out of sequence");
+    DeviceGuard g(x->device);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int par = (int)(x->epoch & 1u), me = x->rank, gi = x->recv_groups;
+    ++x->recv_groups;
+    uint64_t seg_begin[257];
+    uint32_t nseg = 0;
+    uint64_t run = 0;
+    bool started = false;
+    for (int d = 0; d < 256; ++d) {
+        if (x->owner[d] != me) continue;
+        if (x->group[d] == gi) {
+            if (!started) { seg_begin[0] = run; started = true; }
+            seg_begin[++nseg] = run + x->tot[d];
+        }
+        run += x->tot[d];
+    }
+    int rc = wait_flags(x, stream, par, gi);
+    if (rc) return rc;
+    if (!nseg || seg_begin[nseg] == seg_begin[0]) return THRS_OK;
+    int ia = 0;
+    X_THRS(thrs_sort_segments_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals,
+                                 x->seg_scratch, x->seg_scratch_bytes, seg_begin, nseg, 0, x->key_bits - 8, stream, &ia));
+    x->last_launches += (uint32_t)thrs_last_launch_count();
+    x->in_alt = ia;
+    return THRS_OK;
+}
+
+int thrs_xchg_result(thrs_xchg* x, void* stream_, void** out_keys, void** out_values, uint64_t* out_count)
+{
+    if (!x || !out_keys || !out_values || !out_count) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_result: NULL argument");
+    if (x->phase != 2 || x->recv_groups != x->groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_result: groups outstanding");
     x->phase = 0;
     x->began = false;
     DeviceGuard g(x->device);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank;
-    // ---- incoming: as soon as a group is complete, sort its buckets on the remaining low bits
-    int in_alt = 0;
-    for (int gi = 0; gi < x->groups; ++gi) {
-        uint64_t seg_begin[257];
-        uint32_t nseg = 0;
-        uint64_t run = 0;
-        bool started = false;
-        for (int d = 0; d < 256; ++d) {
-            if (x->owner[d] != me) continue;
-            if (x->group[d] == gi) {
-                if (!started) { seg_begin[0] = run; started = true; }
-                seg_begin[++nseg] = run + x->tot[d];
-            }
-            run += x->tot[d];
-        }
-        int rc = wait_flags(x, stream, par, gi);
-        if (rc) return rc;
-        if (!nseg || seg_begin[nseg] == seg_begin[0]) continue;
-        int ia = 0;
-        X_THRS(thrs_sort_segments_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals,
-                                     x->seg_scratch, x->seg_scratch_bytes, seg_begin, nseg, 0, x->key_bits - 8, stream, &ia));
-        x->last_launches += (uint32_t)thrs_last_launch_count();
-        in_alt = ia;
-    }
     // the send buffers may be overwritten by the next sort only after my own copies have left
-    for (int r = 0; r < P; ++r) X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
-    *out_keys = in_alt ? x->alt_keys : x->window + x->off_keys;
-    *out_values = in_alt ? x->alt_vals : x->window + x->off_vals;
-    *out_count = x->recv[me];
-    x->last_recv = x->recv[me];
+    for (int r = 0; r < x->world; ++r) X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
+    *out_keys = x->in_alt ? x->alt_keys : x->window + x->off_keys;
+    *out_values = x->in_alt ? x->alt_vals : x->window + x->off_vals;
+    *out_count = x->recv[x->rank];
+    x->last_recv = x->recv[x->rank];
     return THRS_OK;
 }
 
 int thrs_xchg_finish(thrs_xchg* x, void* stream, void** out_keys, void** out_values, uint64_t* out_count,
                      uint64_t* needed_capacity)
 {
-    int rc = thrs_xchg_send(x, stream, needed_capacity);
+    int groups = 0;
+    int rc = thrs_xchg_plan_step(x, stream, needed_capacity, &groups);
+    for (int g = 0; g < groups && rc == THRS_OK; ++g) {
+        rc = thrs_xchg_send_group(x);
+        if (rc == THRS_OK) rc = thrs_xchg_recv_group(x, stream);
+    }
     if (rc) return rc;
-    return thrs_xchg_recv(x, stream, out_keys, out_values, out_count);
+    return thrs_xchg_result(x, stream, out_keys, out_values, out_count);
 }
 
 int thrs_xchg_stats(thrs_xchg* x, uint64_t* received_items, uint64_t* sent_remote_bytes, uint32_t* kernel_launches,

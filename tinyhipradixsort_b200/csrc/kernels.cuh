@@ -59,11 +59,11 @@ constexpr int SEG_HEADER = 4; // [0] segments, [1] virtual tiles, [2..3] unused
 constexpr int SEG_TABLE_WORDS = SEG_HEADER + 3 * (MAX_SEGMENTS + 1);
 constexpr int SEG_TABLE_BYTES = (SEG_TABLE_WORDS * 4 + 15) & ~15;
 // s_misc words: [0,8) scan scratch, [12..15] tickets of ordinary launches; segmented launches keep the
-// description of a drawn tile in three slots of 8 words: two alternate in the pipelined loop (a slot is
-// read a full iteration after it was written), the third serves a block's first ticket and the
-// straight-line path
+// description of a drawn tile in four slots of 8 words: three rotate in the pipelined loop (a tile's slot
+// is read until its look-back resolves, two iterations after it was drawn), the fourth serves a block's
+// first ticket and the straight-line path.  The kernel keeps only slot indices in registers.
 constexpr int MISC_WORDS = 64;
-constexpr int TILE_SLOT0 = 16, TILE_SLOT_WORDS = 8, TILE_SLOT_LINE = TILE_SLOT0 + 2 * TILE_SLOT_WORDS;
+constexpr int TILE_SLOT0 = 16, TILE_SLOT_WORDS = 8, TILE_SLOT_LINE = TILE_SLOT0 + 3 * TILE_SLOT_WORDS;
 
 // Scratch ("pSumBuffer") layout in u32 words.  Fixed-size control block first, then the
 // look-back status rows of every pass: status[pass][tile][256].
@@ -949,11 +949,11 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     if (!PEER) pdl_wait(); // keys, values and bin bases of the previous launch are complete and visible from here
     __syncthreads();
     uint32_t tile = SEG ? s_misc[TILE_SLOT_LINE] : s_misc[15];
-    SegTile sg, p_sg; // SEG only: the current tile and the one whose read-out is pending
-    if (SEG) sg = seg_tile_read(s_misc + TILE_SLOT_LINE);
+    // SEG only: slots (word offsets into s_misc) describing the current tile and the one whose read-out is pending
+    uint32_t cs = TILE_SLOT_LINE, ps = TILE_SLOT_LINE;
     KeyT key[ITEMS];
     if (SEG) {
-        if (tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, sg.offset, sg.valid);
+        if (tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, s_misc[cs + 2], s_misc[cs + 3]);
     } else if (tile < num_tiles) {
         const size_t tb = (size_t)tile * TILE;
         load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, tb, (n - tb) < (size_t)TILE ? (uint32_t)(n - tb) : (uint32_t)TILE);
@@ -965,28 +965,30 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
     uint32_t iter = 0;
     PHASE_BEGIN();
     while (true) {
-        const bool cur = SEG ? (tile < num_tiles && sg.valid == (uint32_t)TILE) : (tile < full_tiles); // block-uniform
+        const bool cur = SEG ? (tile < num_tiles && s_misc[cs + 3] == (uint32_t)TILE) : (tile < full_tiles); // block-uniform
         if (!cur && !have_prev) {
             if (!SEG || tile >= num_tiles) break;
             // SEG: the partial last tile of a segment and nothing in flight: straight-line path; like an
             // iteration of this loop it leaves the next tile's keys in `key`
             SegTile nx;
+            const SegTile sg = seg_tile_read(s_misc + cs); // by value: the call draws the next tile into the same slot
+            __syncthreads();
             tile = onesweep_tile<false, FAST, PEER, SEG, KeyT, KIND, DESC, VBYTES, THREADS, ITEMS>(
                 key, keys_in, n, num_tiles, ticket, keys_out, vals_in, vals_out, bit, bit_c, status, gsum, gprefix, base_in,
                 base_out, tile, false, (size_t)sg.offset, sg.valid, smem_raw, th, s_seg, sg, &nx);
-            sg = nx;
+            cs = TILE_SLOT_LINE;
             // nothing of the drained pipeline is needed any more: say so, or ptxas keeps the look-back registers
             // alive (and spills them in the hot loop) across the straight-line tile
 #pragma unroll
             for (int i = 0; i < GROUP_TILES - 1; ++i) lb_v[i] = 0u;
 #pragma unroll
             for (int j = 0; j < GROUP_LOOK; ++j) { lb_ga[j] = 0u; lb_gq[j] = 0u; }
-            p_tile = 0; p_count = 0; p_bin_start = 0; p_sg = SegTile();
+            p_tile = 0; p_count = 0; p_bin_start = 0; ps = TILE_SLOT_LINE;
             continue;
         }
         PHASE_MARK(8); // issue of the look-back loads and the key prefetch (waits for phase C's stores to drain)
-        const size_t tile_base = SEG ? (size_t)sg.offset : (size_t)tile * TILE;
-        const uint32_t g0 = SEG ? sg.g0 : 0u;          // first look-back group / first tile of this tile's segment
+        const size_t tile_base = SEG ? (size_t)s_misc[cs + 2] : (size_t)tile * TILE;
+        const uint32_t g0 = SEG ? s_misc[cs + 4] : 0u; // first look-back group / first tile of this tile's segment
         const uint32_t t0 = SEG ? g0 * GROUP_TILES : 0u;
         uint32_t count = 0;
         bool warp_one_digit = false;
@@ -997,7 +999,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (cur) {
             // ticket of the tile after this one (slot alternates: it is read a full iteration later)
             if (SEG) {
-                if (tid == 0) seg_tile_draw<TILE>(ticket, num_tiles, s_seg, s_misc + TILE_SLOT0 + TILE_SLOT_WORDS * (iter & 1u));
+                if (tid == 0) seg_tile_draw<TILE>(ticket, num_tiles, s_seg, s_misc + TILE_SLOT0 + TILE_SLOT_WORDS * (iter % 3u));
             } else if (tid == 0) s_misc[12 + (iter & 1u)] = atomicAdd(ticket, 1u);
 #ifdef THRS_PHASE_TIMING
             if (tid == 0 && s_misc[12 + (iter & 1u)] < 32768u) g_trace[0][s_misc[12 + (iter & 1u)]] = trace_now();
@@ -1093,7 +1095,8 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (have_prev && tid < RADIX) {
             uint32_t excl = 0;
             TRACE(4, p_tile);
-            if (p_tile != (SEG ? p_sg.g0 * GROUP_TILES : 0u)) {
+            const uint32_t p_g0 = SEG ? s_misc[ps + 4] : 0u;
+            if (p_tile != p_g0 * GROUP_TILES) {
                 const uint32_t g = p_tile / GROUP_TILES, r = p_tile % GROUP_TILES;
                 const uint32_t* col = status + tid;
                 const uint32_t* gs = gsum + tid;
@@ -1126,7 +1129,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                     }
                     while (!have) { // beyond the prefetched rows, or a group still filling: poll
                         LB_COUNT(4);
-                        const uint32_t q = gg == (SEG ? p_sg.g0 : 0u) ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
+                        const uint32_t q = gg == p_g0 ? FLAG_PREFIX : ld_relaxed(gp + (size_t)gg * RADIX);
                         if ((q >> FLAG_SHIFT) == 2u) { pg += q & VALUE_MASK; have = true; break; }
                         const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
                         if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
@@ -1137,7 +1140,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                 st_relaxed(status + (size_t)p_tile * RADIX + tid, FLAG_PREFIX | (excl + p_count));
             }
             TRACE(5, p_tile);
-            const uint32_t gbase = base_in[(SEG ? p_sg.seg * RADIX : 0u) + tid] + excl;
+            const uint32_t gbase = base_in[(SEG ? s_misc[ps + 1] * RADIX : 0u) + tid] + excl;
             s_off[tid] = gbase - p_bin_start;
             if (base_out != nullptr && p_tile == num_tiles - 1) base_out[tid] = gbase + p_count;
             if (PEER && tid < 8) {
@@ -1232,9 +1235,8 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         }
 
         // ---- phase C(tile): rank and stage at the tile-sorted position
-        const uint32_t next_tile = SEG ? s_misc[TILE_SLOT0 + TILE_SLOT_WORDS * (iter & 1u)] : s_misc[12 + (iter & 1u)];
-        SegTile next_sg;
-        if (SEG) next_sg = seg_tile_read(s_misc + TILE_SLOT0 + TILE_SLOT_WORDS * (iter & 1u));
+        const uint32_t ns = TILE_SLOT0 + TILE_SLOT_WORDS * (iter % 3u); // SEG: slot of the tile drawn in this iteration
+        const uint32_t next_tile = SEG ? s_misc[ns] : s_misc[12 + (iter & 1u)];
         const uint32_t lane_bit = 1u << lane;
         const uint32_t lane_lt = lane_bit - 1u;
         if (warp_one_digit) {
@@ -1320,13 +1322,13 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
             }
         }
         if (SEG) {
-            if (next_tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, next_sg.offset, next_sg.valid);
+            if (next_tile < num_tiles) load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, s_misc[ns + 2], s_misc[ns + 3]);
         } else if (next_tile < num_tiles) {
             const size_t nb = (size_t)next_tile * TILE;
             load_tile_keys<KeyT, THREADS, ITEMS>(key, keys_in, nb, (n - nb) < (size_t)TILE ? (uint32_t)(n - nb) : (uint32_t)TILE);
         }
         p_tile = tile; p_count = count; p_bin_start = bin_start; have_prev = true;
-        if (SEG) { p_sg = sg; sg = next_sg; }
+        if (SEG) { ps = cs; cs = ns; }
         tile = next_tile;
         ++iter;
     }

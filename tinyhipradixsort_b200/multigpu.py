@@ -518,16 +518,19 @@ def bench(args, dist, rank, world, dev, g):
         edges = torch.searchsorted(k, torch.arange(lo, hi + 2, device=dev, dtype=torch.int64)).tolist()
         del k
         sk, sv = rk.clone(), rv.clone()
-        stmp = torch.empty(srt.getSegmentsTemporaryBufferBytes(cnt, len(edges) - 1, True), dtype=torch.uint8, device=dev)
+        ak, av = torch.empty_like(sk), torch.empty_like(sv)
+        sbytes = srt.getSegmentsScratchBytes(cnt, len(edges) - 1)
+        stmp = torch.empty(sbytes, dtype=torch.uint8, device=dev)
         best = None
-        for _ in range(3):  # already sorted input: the passes move the same bytes, ranking cost is that of 1-digit warps on pass 3 only
+        for _ in range(3):  # unsorted keys inside the same bucket boundaries: the ranking work of the real step
             sk.copy_(keys0[:cnt] if cnt <= n_l else rk)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
-            srt.sortSegments(sk, sv, edges, stmp, 0, 24, stream)
+            srt.sortSegmentsOutOfPlace(sk, sv, ak, av, stmp, sbytes, edges, 0, 24, stream)
             b.record(stream)
             b.synchronize()
             best = a.elapsed_time(b) if best is None else min(best, a.elapsed_time(b))
+        del ak, av
         seg_alone_ms = best
         del sk, sv, stmp
     torch.cuda.empty_cache()

@@ -248,6 +248,21 @@ class RadixSort:
             _check(self._lib.thrs_sort_segments_pairs(self._h, _ptr(keyBuffer), _ptr(valueBuffer), seg, nseg,
                                                       _ptr(temporaryBuffer), int(startBits), int(endBits), _stream(stream)))
 
+    def getSegmentsScratchBytes(self, totalInputs, numberOfSegments):
+        return int(self._lib.thrs_segments_scratch_bytes(self._h, int(totalInputs), int(numberOfSegments)))
+
+    def sortSegmentsOutOfPlace(self, keyBuffer, valueBuffer, altKeyBuffer, altValueBuffer, scratchBuffer, scratchBytes,
+                               segmentBegin, startBits, endBits, stream=None):
+        """thrs_sort_segments_ex: ping-pongs between the arrays and their alternates, no copy-back;
+        returns True if the sorted segments lie in the alternates."""
+        seg = (ctypes.c_uint64 * len(segmentBegin))(*[int(x) for x in segmentBegin])
+        in_alt = ctypes.c_int(0)
+        _check(self._lib.thrs_sort_segments_ex(self._h, _ptr(keyBuffer), None if valueBuffer is None else _ptr(valueBuffer),
+                                               _ptr(altKeyBuffer), None if altValueBuffer is None else _ptr(altValueBuffer),
+                                               _ptr(scratchBuffer), int(scratchBytes), seg, len(segmentBegin) - 1,
+                                               int(startBits), int(endBits), _stream(stream), ctypes.byref(in_alt)))
+        return bool(in_alt.value)
+
     # -- not in the reference: what unittest.cpp:399-414 does around a sort, in one C-ABI call
     def sortHost(self, host_keys, host_values, startBits, endBits):
         """Sort numpy arrays / CPU tensors in place (H2D, sort, D2H inside the call)."""
