@@ -25,6 +25,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 #include <new>
 #include <vector>
 #include "../../include/thrs_b200.h"
@@ -133,6 +134,40 @@ struct DeviceGuard {
     explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
     ~DeviceGuard() { int cur = 0; cudaGetDevice(&cur); if (cur != prev) cudaSetDevice(prev); }
 };
+
+// A group's bucket copies to one destination as ONE batched call (cudaMemcpyBatchAsync, CUDA 12.8+): 128 separate
+// cudaMemcpyAsync calls per destination cost the host several microseconds each — more than the copies take
+// on the wire at 8 GPUs — and the owner's sort cannot be enqueued before them.  Falls back to single copies.
+int copy_batch(std::vector<void*>& dsts, std::vector<void*>& srcs, std::vector<size_t>& sizes, cudaStream_t stream)
+{
+    if (dsts.empty()) return THRS_OK;
+    static int batch_ok = getenv("THRS_XCHG_NO_BATCH") ? 0 : 1;
+    if (batch_ok) {
+        cudaMemcpyAttributes attr;
+        memset(&attr, 0, sizeof(attr));
+        attr.srcAccessOrder = cudaMemcpySrcAccessOrderStream;
+        size_t idx = 0, fail = 0;
+        cudaError_t e = cudaMemcpyBatchAsync(dsts.data(), srcs.data(), sizes.data(), dsts.size(), &attr, &idx, 1, &fail, stream);
+        if (e == cudaSuccess) return THRS_OK;
+        cudaGetLastError();
+        batch_ok = 0; // not supported by this driver: single copies from now on
+    }
+    for (size_t i = 0; i < dsts.size(); ++i)
+        X_CUDA(cudaMemcpyAsync(dsts[i], srcs[i], sizes[i], cudaMemcpyDefault, stream), "bucket copy");
+    return THRS_OK;
+}
+
+double host_us()
+{
+    timespec t;
+    clock_gettime(CLOCK_MONOTONIC, &t);
+    return t.tv_sec * 1e6 + t.tv_nsec * 1e-3;
+}
+bool trace_on()
+{
+    static int on = getenv("THRS_XCHG_TRACE") ? 1 : 0;
+    return on != 0;
+}
 
 int wait_flags(thrs_xchg* x, cudaStream_t stream, int parity, int slot)
 {
@@ -362,7 +397,9 @@ int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, 
         X_CUDA(cudaMemcpyAsync(x->h_counts + (size_t)s * 256, x->counts_ptr(x->window, par, s), 1024, cudaMemcpyDeviceToHost, x->side),
                "read counts");
     X_CUDA(cudaEventRecord(x->ev_host, x->side), "cudaEventRecord");
+    const double t_sync0 = host_us();
     X_CUDA(cudaEventSynchronize(x->ev_host), "waiting for the gathered histograms");
+    if (trace_on()) fprintf(stderr, "[xchg r%d] plan: waited %.0f us for the gathered counts\n", me, host_us() - t_sync0);
 
     std::vector<uint64_t> counts((size_t)P * 256);
     for (size_t i = 0; i < counts.size(); ++i) counts[i] = x->h_counts[i];
@@ -413,27 +450,36 @@ int thrs_xchg_send_group(thrs_xchg* x)
     if (!x || x->phase != 2 || x->sent_groups >= x->groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send_group: out of sequence");
     DeviceGuard g(x->device);
     const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank, gi = x->sent_groups;
+    const double t0 = host_us();
+    std::vector<void*> dk, sk, dv, sv;
+    std::vector<size_t> zk, zv;
     for (int i = 1; i <= P; ++i) {
         const int r = (me + i) % P; // the own rank last: local copies are the cheapest to delay
-        bool any = false;
+        dk.clear(); sk.clear(); dv.clear(); sv.clear(); zk.clear(); zv.clear();
         for (int d = 0; d < 256; ++d) {
             if (x->owner[d] != r || x->group[d] != gi) continue;
             const uint64_t c = x->my_counts[d];
             if (!c) continue;
-            X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + x->land[d] * x->kbytes, x->send_keys + x->send_base[d] * x->kbytes,
-                                   c * x->kbytes, cudaMemcpyDefault, x->copy[r]), "bucket copy (keys)");
-            X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_vals + x->land[d] * x->vbytes, x->send_vals + x->send_base[d] * x->vbytes,
-                                   c * x->vbytes, cudaMemcpyDefault, x->copyv[r]), "bucket copy (values)");
+            dk.push_back(x->peer[r] + x->off_keys + x->land[d] * x->kbytes);
+            sk.push_back(x->send_keys + x->send_base[d] * x->kbytes);
+            zk.push_back(c * x->kbytes);
+            dv.push_back(x->peer[r] + x->off_vals + x->land[d] * x->vbytes);
+            sv.push_back(x->send_vals + x->send_base[d] * x->vbytes);
+            zv.push_back(c * x->vbytes);
             if (r != me) x->last_sent_remote_bytes += c * (uint64_t)(x->kbytes + x->vbytes);
             x->last_copies += 2;
-            any = true;
         }
+        const bool any = !dk.empty();
+        int rc = copy_batch(dk, sk, zk, x->copy[r]);
+        if (rc == THRS_OK) rc = copy_batch(dv, sv, zv, x->copyv[r]);
+        if (rc) return rc;
         if (any) { // the flag follows BOTH streams
             X_CUDA(cudaEventRecord(x->ev_copyv[r], x->copyv[r]), "cudaEventRecord");
             X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_copyv[r], 0), "cudaStreamWaitEvent");
         }
         X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDefault, x->copy[r]), "group flag");
     }
+    if (trace_on()) fprintf(stderr, "[xchg r%d] send_group %d: host %.0f us\n", me, gi, host_us() - t0);
     ++x->sent_groups;
     if (x->sent_groups == x->groups)
         for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
@@ -460,12 +506,14 @@ int thrs_xchg_recv_group(thrs_xchg* x, void* stream_)
         }
         run += x->tot[d];
     }
+    const double t0 = host_us();
     int rc = wait_flags(x, stream, par, gi);
     if (rc) return rc;
     if (!nseg || seg_begin[nseg] == seg_begin[0]) return THRS_OK;
     int ia = 0;
     X_THRS(thrs_sort_segments_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals,
                                  x->seg_scratch, x->seg_scratch_bytes, seg_begin, nseg, 0, x->key_bits - 8, stream, &ia));
+    if (trace_on()) fprintf(stderr, "[xchg r%d] recv_group %d: host %.0f us (%u buckets)\n", me, gi, host_us() - t0, nseg);
     x->last_launches += (uint32_t)thrs_last_launch_count();
     x->in_alt = ia;
     return THRS_OK;
