@@ -172,6 +172,18 @@ THRS_API int thrs_sort_segments_keys(thrs_sorter* s, void* keys, const uint64_t*
 THRS_API int thrs_sort_segments_pairs(thrs_sorter* s, void* keys, void* values, const uint64_t* seg_begin, uint32_t nseg,
                                       void* temp, int start_bits, int end_bits, void* stream);
 THRS_API uint64_t thrs_segments_scratch_bytes(const thrs_sorter* s, uint64_t n_total, uint32_t nseg);
+/* The gathering form: the input is nchunk <= 256 contiguous CHUNKS (chunk_begin, nchunk + 1 ascending
+ * host offsets), chunk i belongs to output bucket chunk_bucket[i]; the output is nbucket <= 256
+ * contiguous BUCKETS (bucket_begin) covering the same range, every bucket as large as its chunks
+ * together.  Bucket b comes out as the stable sort, on bits [start_bits, end_bits), of its chunks
+ * concatenated in index order.  Pass 0 reads the chunk layout and writes the bucket layout (the
+ * gather costs no extra pass); at least one pass.  Otherwise like thrs_sort_segments_ex, scratch of
+ * thrs_segments_scratch_bytes(s, chunk_begin[nchunk], 256) bytes.  This is how a rank of the
+ * multi-GPU sort merges the per-source chunks of its top-digit buckets while sorting them. */
+THRS_API int thrs_sort_buckets_ex(thrs_sorter* s, void* keys, void* values, void* alt_keys, void* alt_values, void* scratch,
+                                  uint64_t scratch_bytes, const uint64_t* chunk_begin, const uint32_t* chunk_bucket,
+                                  uint32_t nchunk, const uint64_t* bucket_begin, uint32_t nbucket, int start_bits,
+                                  int end_bits, void* stream, int* result_in_alt);
 THRS_API int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_keys, void* alt_values, void* scratch,
                                    uint64_t scratch_bytes, const uint64_t* seg_begin, uint32_t nseg, int start_bits,
                                    int end_bits, void* stream, int* result_in_alt);
@@ -216,12 +228,14 @@ THRS_API int thrs_ipc_close(void* device_ptr);
  *                     side stream pushes the 256 counts into every rank's window with the copy engines
  *                     and reads the gathered table back (no NCCL, no SM).  Returns without waiting.
  *   thrs_xchg_finish  waits (host) for the gathered table, picks splitters on digit boundaries (equal
- *                     keys never straddle ranks), and enqueues: copy-engine copies of every (digit,
- *                     source) chunk straight into the owner's window, DIGIT-MAJOR / SOURCE-MINOR, group
- *                     by group, a 4-byte flag after each group; on `stream`, per group, a
- *                     cuStreamWaitValue32 on the group's flags and a segmented sort
- *                     (thrs_sort_segments_ex, one segment per digit) on bits [0, key bits - 8) while
- *                     later groups are still in flight.  Returns device pointers (owned by the
+ *                     keys never straddle ranks), cuts every owner's digits into a few groups of
+ *                     consecutive digits and enqueues, group by group: ONE copy-engine copy of keys and
+ *                     one of values per destination (a group's digits are adjacent in the digit-ordered
+ *                     send buffers) straight into the owner's window, then a 4-byte flag; on `stream`,
+ *                     per group, a cuStreamWaitValue32 on the group's flags and thrs_sort_buckets_ex
+ *                     on bits [0, key bits - 8): its pass 0 gathers the group's (source, digit) chunks
+ *                     into digit buckets, so the merge of the sources costs no extra pass, and it runs
+ *                     while later groups are still in flight.  Returns device pointers (owned by the
  *                     context, valid until its next begin) to this rank's sorted share.
  * Concatenating the shares of rank 0..world-1 is exactly std::stable_sort of the concatenated slices
  * (ties in (rank, position) order).  Every rank must call begin / finish the same number of times
@@ -256,7 +270,7 @@ THRS_API int thrs_xchg_result(thrs_xchg* x, void* stream, void** out_keys, void*
 THRS_API int thrs_xchg_stats(thrs_xchg* x, uint64_t* received_items, uint64_t* sent_remote_bytes, uint32_t* kernel_launches,
                              uint32_t* bucket_copies);
 THRS_API int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner_of_digit, uint64_t* recv_totals,
-                            int32_t* group_of_digit);
+                            int32_t* group_of_digit, int32_t* groups_of_rank);
 THRS_API const char* thrs_xchg_last_error(void);
 
 /* Single-process multi-GPU sort (SURVEY.md 8(b) plan: thrs_mg_create / thrs_mg_sort_pairs /

@@ -1,5 +1,5 @@
 #!/bin/bash
-# quick multi-GPU A/B: gpu_job_mg2.sh N TAG  -> exchange with batch copies (trace on one run), groups 4/8, no-batch
+# quick multi-GPU A/B: gpu_job_mg2.sh N TAG  -> exchange with 4 / 8 / 16 groups, one run with the host trace
 N=$1; TAG=$2
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
@@ -21,6 +21,6 @@ run g8 THRS_MG_GROUPS=8
 run g4 THRS_MG_GROUPS=4
 run g16 THRS_MG_GROUPS=16
 run g8_trace THRS_MG_GROUPS=8 THRS_XCHG_TRACE=1
-run g8_nobatch THRS_MG_GROUPS=8 THRS_XCHG_NO_BATCH=1 THRS_XCHG_TRACE=1
+
 grep "xchg r0" gpurun_out/${TAG}_g8_trace.err | tail -20
-grep "xchg r0" gpurun_out/${TAG}_g8_nobatch.err | tail -18
+

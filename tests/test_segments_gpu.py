@@ -140,3 +140,46 @@ def test_large_segments_property_2pow27():
     assert bool((k0[v.to(torch.int64)] == k).all())
     seg_of = torch.bucketize(torch.arange(n, device="cuda"), torch.tensor(cuts[1:-1], device="cuda"), right=True)
     assert bool((seg_of[v.to(torch.int64)] == seg_of).all()), "an item left its segment"
+
+
+@pytest.mark.parametrize("nsrc,nb,ranking", [(2, 128, thrs.RadixSort.RANKING_COUNTER_RETURN), (8, 32, thrs.RadixSort.RANKING_COUNTER_RETURN),
+                                            (3, 7, thrs.RadixSort.RANKING_MATCH_MASK), (1, 5, thrs.RadixSort.RANKING_COUNTER_RETURN)])
+def test_buckets_gather_source_major_chunks(nsrc, nb, ranking):
+    """thrs_sort_buckets_ex: the layout a rank of the multi-GPU sort receives — nsrc sources, each a run of nb
+    chunks (one per bucket) — must come out as nb buckets, bucket b = stable sort on bits [0,24) of its
+    chunks concatenated in source order.  Chunk sizes are uneven, some empty, some larger than a tile."""
+    s = make_sorter("u32", 4)
+    s.setRanking(ranking)
+    t = s.tileItems()
+    rng = oracle.SplitMix64(100 * nsrc + nb)
+    sizes = [[int(rng.next() % (3 * t // 2)) if (rng.next() % 5) else 0 for _ in range(nb)] for _ in range(nsrc)]
+    sizes[0][0] = 2 * t + 5
+    chunk_begin, chunk_bucket = [13], []
+    for src in range(nsrc):
+        for b in range(nb):
+            chunk_begin.append(chunk_begin[-1] + sizes[src][b])
+            chunk_bucket.append(b)
+    bucket_begin = [13]
+    for b in range(nb):
+        bucket_begin.append(bucket_begin[-1] + sum(sizes[src][b] for src in range(nsrc)))
+    n = chunk_begin[-1] + 9
+    keys = rng.randomize("u32", n, mode=1)
+    keys[::2] &= np.uint32(0x00030303)  # heavy duplicates on the sorted bits: cross-chunk stability is observable
+    vals = _values(n, 4)
+    dk, dv = to_device(keys), to_device(vals)
+    ak, av = torch.empty_like(dk), torch.empty_like(dv)
+    ak.fill_(-1); av.fill_(-1)
+    sb = s.getSegmentsScratchBytes(n, 256)
+    scratch = torch.empty(sb, dtype=torch.uint8, device="cuda")
+    scratch.fill_(0xA5)
+    in_alt = s.sortBucketsOutOfPlace(dk, dv, ak, av, scratch, sb, chunk_begin, chunk_bucket, bucket_begin, 0, 24)
+    torch.cuda.synchronize()
+    assert in_alt, "three passes end in the alternates"
+    got_k, got_v = to_host(ak, keys), to_host(av, vals)
+    for b in range(nb):
+        idx = np.concatenate([np.arange(chunk_begin[src * nb + b], chunk_begin[src * nb + b + 1]) for src in range(nsrc)]).astype(np.int64)
+        if idx.size == 0:
+            continue
+        ek, ev = oracle.sort("u32", keys[idx], vals[idx], 0, 24)
+        assert np.array_equal(got_k[bucket_begin[b]:bucket_begin[b + 1]], ek), f"bucket {b}: keys"
+        assert np.array_equal(got_v[bucket_begin[b]:bucket_begin[b + 1]], ev), f"bucket {b}: values (stability across chunks)"

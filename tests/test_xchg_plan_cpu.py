@@ -18,12 +18,13 @@ def _plan(world, groups, counts):
     c = np.ascontiguousarray(counts, dtype=np.uint64).reshape(world * 256)
     owner = np.zeros(256, dtype=np.int32)
     group = np.zeros(256, dtype=np.int32)
+    ngroups = np.zeros(world, dtype=np.int32)
     recv = np.zeros(world, dtype=np.uint64)
     rc = lib.thrs_xchg_plan(world, groups, c.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
                             owner.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), recv.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
-                            group.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)))
+                            group.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), ngroups.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)))
     assert rc == 0
-    return owner, recv, group
+    return owner, recv, group, ngroups
 
 
 @pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
@@ -40,14 +41,17 @@ def test_plan_matches_numpy_reference(world):
             counts[:] = 0              # empty input
         if case == 4:
             counts[:, ::2] = 0
-        owner, recv, group = _plan(world, 4, counts)
+        owner, recv, group, ngroups = _plan(world, 4, counts)
         dest, send = plan_partition(counts.astype(np.int64), world)
         assert np.array_equal(owner, dest)
         assert np.array_equal(recv.astype(np.int64), send.sum(axis=0))
         assert np.all(np.diff(owner) >= 0), "owners must be monotone in the digit"
-        for r in range(world):  # groups restart at every owner and are monotone inside it
+        for r in range(world):  # groups restart at every owner, step by at most one, and hold <= 256 / world digits
             g = group[owner == r]
-            assert g.size == 0 or (g[0] == 0 and np.all(np.diff(g) >= 0) and g.max() < 4)
+            assert ngroups[r] == (0 if g.size == 0 else g.max() + 1)
+            if g.size:
+                assert g[0] == 0 and np.all(np.diff(g) >= 0) and np.all(np.diff(g) <= 1) and g.max() < 4 + world
+                assert np.bincount(g).max() <= 256 // world, "a group is sorted as world x digits <= 256 chunks"
 
 
 @pytest.mark.parametrize("world,key", [(2, "u32"), (3, "f32"), (8, "u32"), (4, "u64")])
@@ -68,25 +72,26 @@ def test_cpu_emulation_of_the_exchange_equals_stable_sort(world, key):
         d = np.array([oracle.field(key, int(x), bits - 8, bits) for x in pk], dtype=np.int64)
         counts[r] = np.bincount(d, minlength=256)
         part.append((pk, pv, d))
-    owner, recv, group = _plan(world, 4, counts)
+    owner, recv, group, ngroups = _plan(world, 4, counts)
     out_k, out_v = [], []
     for r in range(world):
-        # digit-major / source-minor: what the copy engines assemble in rank r's window
-        ck, cv, seg = [], [], [0]
-        for d in range(256):
-            if owner[d] != r:
-                continue
-            for s in range(world):
-                m = part[s][2] == d
-                ck.append(part[s][0][m])
-                cv.append(part[s][1][m])
-            seg.append(seg[-1] + int(counts[:, d].sum()))
-        rk = np.concatenate(ck) if ck else np.zeros(0, dtype=slices[0].dtype)
-        rv = np.concatenate(cv) if cv else np.zeros(0, dtype=np.uint32)
+        rk_parts, rv_parts = [], []
+        for g in range(int(ngroups[r])):
+            digits = [d for d in range(256) if owner[d] == r and group[d] == g]
+            # what the copy engines assemble in rank r's window for this group: SOURCE-major, digit-minor
+            # (one contiguous copy per source), then thrs_sort_buckets_ex: bucket d = its chunks in source
+            # order, sorted stably on the low bits
+            for d in digits:
+                ck = [part[s][0][part[s][2] == d] for s in range(world)]
+                cv = [part[s][1][part[s][2] == d] for s in range(world)]
+                bk, bv = np.concatenate(ck), np.concatenate(cv)
+                if bk.size:
+                    bk, bv = oracle.sort(key, bk, bv, 0, bits - 8)
+                rk_parts.append(bk)
+                rv_parts.append(bv)
+        rk = np.concatenate(rk_parts) if rk_parts else np.zeros(0, dtype=slices[0].dtype)
+        rv = np.concatenate(rv_parts) if rv_parts else np.zeros(0, dtype=np.uint32)
         assert rk.shape[0] == int(recv[r])
-        for a, b in zip(seg[:-1], seg[1:]):  # segmented sort on the low bits (thrs_sort_segments_ex)
-            if b > a:
-                rk[a:b], rv[a:b] = oracle.sort(key, rk[a:b], rv[a:b], 0, bits - 8)
         out_k.append(rk)
         out_v.append(rv)
     ek, ev = oracle.sort(key, np.concatenate(slices), np.concatenate(vals), 0, bits)

@@ -721,15 +721,21 @@ int thrs_scatter_pairs(thrs_sorter* s, const void* keys, const void* values, uin
 // ---------------------------------------------------------------------------------------------------
 namespace {
 struct SegScratch {
+    // [chunk table | bucket table | chunk -> bucket map | tickets | hist[chunks][passes][256] | base0[chunks][256] |
+    //  base[passes-1][buckets][256] | status rows of pass 0 (chunk tiles) | status rows of passes 1.. (bucket tiles)]
     static constexpr uint64_t TABLE_WORDS = (SEG_TABLE_BYTES / 4);
+    static constexpr uint64_t MAP_WORDS = MAX_SEGMENTS;
     static constexpr uint64_t TICKET_WORDS = 16;
+    static constexpr uint64_t HEAD_WORDS = 2 * TABLE_WORDS + MAP_WORDS;
     static uint64_t vtiles_bound(uint64_t n_total, uint64_t nseg_batch, uint32_t tile)
     {
         return n_total / tile + (uint64_t)(GROUP_TILES + 1) * nseg_batch + GROUP_TILES;
     }
-    static uint64_t words(uint64_t vtiles, uint64_t nseg_batch, uint64_t passes)
+    static uint64_t row_words(uint64_t vtiles) { return (vtiles + 2 * (vtiles / GROUP_TILES + 1)) * RADIX; }
+    static uint64_t words(uint64_t vtiles_chunks, uint64_t vtiles_buckets, uint64_t nchunk, uint64_t nbucket, uint64_t passes)
     {
-        return TABLE_WORDS + TICKET_WORDS + 2 * nseg_batch * passes * RADIX + passes * (vtiles + 2 * (vtiles / GROUP_TILES + 1)) * RADIX;
+        return HEAD_WORDS + TICKET_WORDS + nchunk * passes * RADIX + nchunk * RADIX + (passes - 1) * nbucket * RADIX +
+               row_words(vtiles_chunks) + (passes - 1) * row_words(vtiles_buckets);
     }
 };
 uint32_t min_tile_of(const thrs_sorter* s)
@@ -741,13 +747,144 @@ uint32_t min_tile_of(const thrs_sorter* s)
     }
     return t_min;
 }
+// virtual tile ranges start at whole look-back groups; returns the number of virtual tiles
+uint32_t fill_seg_table(uint32_t* table, const uint64_t* begin64, uint32_t ns, uint32_t tile)
+{
+    std::fill(table, table + SegScratch::TABLE_WORDS, 0u);
+    uint32_t* vt_first = table + SEG_HEADER;
+    uint32_t* begin = vt_first + (MAX_SEGMENTS + 1);
+    uint32_t* count = begin + (MAX_SEGMENTS + 1);
+    uint64_t vt = 0;
+    for (uint32_t i = 0; i < ns; ++i) {
+        const uint64_t c = begin64[i + 1] - begin64[i];
+        vt_first[i] = (uint32_t)vt;
+        begin[i] = (uint32_t)begin64[i];
+        count[i] = (uint32_t)c;
+        vt += div_up(div_up(c, tile), GROUP_TILES) * GROUP_TILES;
+    }
+    vt_first[ns] = (uint32_t)vt;
+    begin[ns] = (uint32_t)begin64[ns];
+    table[0] = ns;
+    table[1] = (uint32_t)vt;
+    return (uint32_t)vt;
+}
 } // namespace
 
 uint64_t thrs_segments_scratch_bytes(const thrs_sorter* s, uint64_t n_total, uint32_t nseg)
 {
     if (!s) return 0;
     const uint64_t batch = nseg < (uint32_t)MAX_SEGMENTS ? (nseg ? nseg : 1) : MAX_SEGMENTS;
-    return align16(4ull * SegScratch::words(SegScratch::vtiles_bound(n_total, batch, min_tile_of(s)), batch, (uint64_t)s->kbytes));
+    const uint64_t vt = SegScratch::vtiles_bound(n_total, batch, min_tile_of(s));
+    return align16(4ull * SegScratch::words(vt, vt, batch, batch, (uint64_t)s->kbytes));
+}
+
+// One batch: nchunk <= 256 input chunks (contiguous, ascending) are sorted into nbucket <= 256 output buckets
+// (contiguous, ascending, same overall extent).  chunk_bucket[i] names the bucket of chunk i; the chunks of
+// one bucket keep their index order (stability across chunks).  Pass 0 reads the chunk layout and writes
+// the bucket layout; later passes run bucket by bucket.  nchunk == nbucket with the identity map is the
+// plain segmented sort.
+static int sort_buckets_batch(thrs_sorter* s, const DeviceState& ds, int fast, bool pairs, char* keys, char* values, char* alt_keys,
+                              char* alt_values, void* scratch, uint64_t scratch_bytes, const uint64_t* chunk_begin,
+                              const uint32_t* chunk_bucket, uint32_t nchunk, const uint64_t* bucket_begin, uint32_t nbucket,
+                              int start_bits, int passes, cudaStream_t stream)
+{
+    const int vslot = pairs ? s->vslot : 0;
+    const uint32_t tile = s->table->tile_items[fast][vslot];
+    // a pinned slot for this batch's tables (reused SEG_RING batches later, after its upload completed)
+    uint32_t* host = nullptr;
+    cudaEvent_t table_ev = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(s->seg_mu);
+        if (!s->seg_host) CUDA_TRY(cudaMallocHost(&s->seg_host, (size_t)thrs_sorter::SEG_RING * SegScratch::HEAD_WORDS * 4), "cudaMallocHost(segment tables)");
+        const int slot = s->seg_next;
+        s->seg_next = (slot + 1) % thrs_sorter::SEG_RING;
+        if (!s->seg_ev[slot]) CUDA_TRY(cudaEventCreateWithFlags(&s->seg_ev[slot], cudaEventDisableTiming), "cudaEventCreate");
+        else CUDA_TRY(cudaEventSynchronize(s->seg_ev[slot]), "cudaEventSynchronize(segment table slot)");
+        host = s->seg_host + (size_t)slot * SegScratch::HEAD_WORDS;
+        table_ev = s->seg_ev[slot];
+    }
+    const uint64_t vtA = fill_seg_table(host, chunk_begin, nchunk, tile);
+    const uint64_t vtB = fill_seg_table(host + SegScratch::TABLE_WORDS, bucket_begin, nbucket, tile);
+    uint32_t* map = host + 2 * SegScratch::TABLE_WORDS;
+    for (uint32_t i = 0; i < (uint32_t)MAX_SEGMENTS; ++i) map[i] = i < nchunk ? chunk_bucket[i] : 0xffffffffu;
+    if (chunk_begin[nchunk] == chunk_begin[0]) { // nothing but empty chunks
+        CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
+        return THRS_OK;
+    }
+    if (4ull * SegScratch::words(vtA, vtB, nchunk, nbucket, passes) > scratch_bytes)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: scratch too small (thrs_segments_scratch_bytes)");
+    uint32_t* w = static_cast<uint32_t*>(scratch);
+    uint32_t* d_tableA = w;
+    uint32_t* d_tableB = d_tableA + SegScratch::TABLE_WORDS;
+    uint32_t* d_map = d_tableB + SegScratch::TABLE_WORDS;
+    uint32_t* d_ticket = d_map + SegScratch::MAP_WORDS;
+    uint32_t* d_hist = d_ticket + SegScratch::TICKET_WORDS;
+    uint32_t* d_base0 = d_hist + (uint64_t)nchunk * passes * RADIX;
+    uint32_t* d_baseP = d_base0 + (uint64_t)nchunk * RADIX;
+    uint32_t* d_rows0 = d_baseP + (uint64_t)(passes - 1) * nbucket * RADIX;
+    uint32_t* d_rowsP = d_rows0 + SegScratch::row_words(vtA);
+    CUDA_TRY(cudaMemcpyAsync(d_tableA, host, 4ull * SegScratch::HEAD_WORDS, cudaMemcpyHostToDevice, stream), "upload segment tables");
+    CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
+    // zero: tickets and histograms (bases are overwritten), then the status rows of all passes
+    CUDA_TRY(launch_zero(d_ticket, 4ull * (SegScratch::TICKET_WORDS + (uint64_t)nchunk * passes * RADIX), ds.sm_count, stream), "zero_kernel launch");
+    CUDA_TRY(launch_zero(d_rows0, 4ull * (SegScratch::row_words(vtA) + (uint64_t)(passes - 1) * SegScratch::row_words(vtB)), ds.sm_count, stream),
+             "zero_kernel launch");
+    g_launches += 2;
+    {
+        const uint64_t span = chunk_begin[nchunk] - chunk_begin[0];
+        uint64_t grid = div_up(span, 1ull << 16);
+        if (grid > (uint64_t)ds.sm_count) grid = ds.sm_count;
+        if (grid == 0) grid = 1;
+        CUDA_TRY(s->table->seg_histogram(keys, d_tableA, d_tableB, d_map, (uint32_t)start_bits, passes, d_hist, d_base0, d_baseP,
+                                         (int)nbucket, (int)grid, stream), "seg_histogram_kernel launch");
+        g_launches += 2;
+    }
+    char* k_in = keys;
+    char* k_out = alt_keys;
+    char* v_in = values;
+    char* v_out = alt_values;
+    for (int p = 0; p < passes; ++p) {
+        const uint64_t vt = p == 0 ? vtA : vtB;
+        OnesweepArgs a;
+        a.keys_in = k_in;
+        a.keys_out = k_out;
+        a.vals_in = pairs ? v_in : nullptr;
+        a.vals_out = pairs ? v_out : nullptr;
+        a.n = (uint32_t)chunk_begin[nchunk];
+        a.bit = (uint32_t)(start_bits + 8 * p);
+        a.status = p == 0 ? d_rows0 : d_rowsP + (uint64_t)(p - 1) * SegScratch::row_words(vtB);
+        a.gsum = a.status + vt * RADIX;
+        a.gprefix = a.gsum + (vt / GROUP_TILES + 1) * RADIX;
+        a.ticket = d_ticket + p;
+        a.sm_count = ds.sm_count;
+        a.base_in = p == 0 ? d_base0 : d_baseP + (uint64_t)(p - 1) * nbucket * RADIX;
+        a.base_out = nullptr;
+        a.pdl = false;
+        a.seg_table = p == 0 ? d_tableA : d_tableB;
+        a.seg_vtiles = (uint32_t)vt;
+        CUDA_TRY(s->table->onesweep_seg[fast][vslot](a, stream), "onesweep_kernel (segmented) launch");
+        ++g_launches;
+        char* t = k_in; k_in = k_out; k_out = t;
+        t = v_in; v_in = v_out; v_out = t;
+    }
+    return THRS_OK;
+}
+
+static int check_buckets_call(thrs_sorter* s, const void* keys, const void* values, const void* alt_keys, const void* alt_values,
+                              const void* scratch, int start_bits, int end_bits, int* passes_out)
+{
+    if (start_bits < 0 || end_bits < start_bits) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_segments: need 0 <= startBits <= endBits");
+    if (((end_bits - start_bits) % 8) != 0) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_segments: (endBits - startBits) must be a multiple of 8");
+    const bool pairs = values != nullptr;
+    if (!keys || !alt_keys || !scratch || (pairs && !alt_values)) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL buffer");
+    if (((uintptr_t)keys % s->kbytes) != 0 || ((uintptr_t)alt_keys % s->kbytes) != 0 || ((uintptr_t)scratch % 16) != 0 ||
+        (pairs && (((uintptr_t)values % s->vbytes) != 0 || ((uintptr_t)alt_values % s->vbytes) != 0)))
+        return fail(THRS_ERR_ALIGNMENT, "thrs_sort_segments: misaligned buffer");
+    const int key_bits = s->kbytes * 8;
+    int passes = 0;
+    for (int b = start_bits; b < end_bits && b < key_bits; b += 8) ++passes;
+    *passes_out = passes;
+    return THRS_OK;
 }
 
 int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_keys, void* alt_values, void* scratch,
@@ -758,129 +895,82 @@ int thrs_sort_segments_ex(thrs_sorter* s, void* keys, void* values, void* alt_ke
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (result_in_alt) *result_in_alt = 0;
     if (!s || !seg_begin) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL argument");
-    if (start_bits < 0 || end_bits < start_bits) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_segments: need 0 <= startBits <= endBits");
-    if (((end_bits - start_bits) % 8) != 0) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_segments: (endBits - startBits) must be a multiple of 8");
-    const bool pairs = values != nullptr;
     for (uint32_t i = 0; i < nseg; ++i) {
         if (seg_begin[i + 1] < seg_begin[i]) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: seg_begin must ascend");
         if (seg_begin[i + 1] - seg_begin[i] > (uint64_t)VALUE_MASK) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: a segment must stay below 2^30 items");
     }
     if (nseg == 0 || seg_begin[nseg] == seg_begin[0] || start_bits == end_bits) return THRS_OK;
     if (seg_begin[nseg] > 0xffffffffull) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: offsets must stay below 2^32");
-    if (!keys || !alt_keys || !scratch || (pairs && !alt_values)) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: NULL buffer");
-    if (((uintptr_t)keys % s->kbytes) != 0 || ((uintptr_t)alt_keys % s->kbytes) != 0 || ((uintptr_t)scratch % 16) != 0 ||
-        (pairs && (((uintptr_t)values % s->vbytes) != 0 || ((uintptr_t)alt_values % s->vbytes) != 0)))
-        return fail(THRS_ERR_ALIGNMENT, "thrs_sort_segments: misaligned buffer");
-    const int key_bits = s->kbytes * 8;
     int passes = 0;
-    for (int b = start_bits; b < end_bits && b < key_bits; b += 8) ++passes;
+    int rc = check_buckets_call(s, keys, values, alt_keys, alt_values, scratch, start_bits, end_bits, &passes);
+    if (rc) return rc;
     if (passes == 0) return THRS_OK;
     const DeviceState* ds = nullptr;
-    int prc = prepare_device(s, &ds);
-    if (prc) return prc;
+    if ((rc = prepare_device(s, &ds))) return rc;
     const int fast = resolve_fast(s, *ds);
-    const int vslot = pairs ? s->vslot : 0;
-    const uint32_t tile = s->table->tile_items[fast][vslot];
-
+    const bool pairs = values != nullptr;
+    uint32_t identity[MAX_SEGMENTS];
+    for (int i = 0; i < MAX_SEGMENTS; ++i) identity[i] = (uint32_t)i;
     for (uint32_t first_seg = 0; first_seg < nseg; first_seg += MAX_SEGMENTS) {
         const uint32_t ns = nseg - first_seg < (uint32_t)MAX_SEGMENTS ? nseg - first_seg : (uint32_t)MAX_SEGMENTS;
-        // a pinned slot for this batch's table (reused SEG_RING batches later, after its upload completed)
-        uint32_t* table = nullptr;
-        cudaEvent_t table_ev = nullptr;
-        {
-            std::lock_guard<std::mutex> lock(s->seg_mu);
-            if (!s->seg_host) CUDA_TRY(cudaMallocHost(&s->seg_host, (size_t)thrs_sorter::SEG_RING * SegScratch::TABLE_WORDS * 4), "cudaMallocHost(segment tables)");
-            const int slot = s->seg_next;
-            s->seg_next = (slot + 1) % thrs_sorter::SEG_RING;
-            if (!s->seg_ev[slot]) CUDA_TRY(cudaEventCreateWithFlags(&s->seg_ev[slot], cudaEventDisableTiming), "cudaEventCreate");
-            else CUDA_TRY(cudaEventSynchronize(s->seg_ev[slot]), "cudaEventSynchronize(segment table slot)");
-            table = s->seg_host + (size_t)slot * SegScratch::TABLE_WORDS;
-            table_ev = s->seg_ev[slot];
-        }
-        // table of this batch: virtual tile ranges start at whole groups
-        std::fill(table, table + SegScratch::TABLE_WORDS, 0u);
-        uint32_t* vt_first = table + SEG_HEADER;
-        uint32_t* begin = vt_first + (MAX_SEGMENTS + 1);
-        uint32_t* count = begin + (MAX_SEGMENTS + 1);
-        uint64_t vt = 0;
-        for (uint32_t i = 0; i < ns; ++i) {
-            const uint64_t c = seg_begin[first_seg + i + 1] - seg_begin[first_seg + i];
-            vt_first[i] = (uint32_t)vt;
-            begin[i] = (uint32_t)seg_begin[first_seg + i];
-            count[i] = (uint32_t)c;
-            vt += div_up(div_up(c, tile), GROUP_TILES) * GROUP_TILES;
-        }
-        vt_first[ns] = (uint32_t)vt;
-        begin[ns] = (uint32_t)seg_begin[first_seg + ns];
-        table[0] = ns;
-        table[1] = (uint32_t)vt;
-        if (begin[ns] == begin[0]) { // only empty segments
-            CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
-            continue;
-        }
-        const uint64_t vtiles = vt, vgroups = vt / GROUP_TILES + 1;
-        if (4ull * SegScratch::words(vtiles, ns, passes) > scratch_bytes)
-            return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_segments: scratch too small (thrs_segments_scratch_bytes)");
-        uint32_t* w = static_cast<uint32_t*>(scratch);
-        uint32_t* d_table = w;
-        uint32_t* d_ticket = d_table + SegScratch::TABLE_WORDS;
-        uint32_t* d_hist = d_ticket + SegScratch::TICKET_WORDS;
-        uint32_t* d_base = d_hist + (uint64_t)ns * passes * RADIX;
-        uint32_t* d_pass = d_base + (uint64_t)ns * passes * RADIX;
-        const uint64_t pass_words = (vtiles + 2 * vgroups) * RADIX;
-        CUDA_TRY(cudaMemcpyAsync(d_table, table, 4ull * SegScratch::TABLE_WORDS, cudaMemcpyHostToDevice, stream), "upload segment table");
-        CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
-        // zero: tickets, histograms (bases are overwritten), status rows of the passes
-        CUDA_TRY(launch_zero(d_ticket, 4ull * (SegScratch::TICKET_WORDS + (uint64_t)ns * passes * RADIX), ds->sm_count, stream), "zero_kernel launch");
-        CUDA_TRY(launch_zero(d_pass, 4ull * passes * pass_words, ds->sm_count, stream), "zero_kernel launch");
-        g_launches += 2;
-        char* k_in = static_cast<char*>(keys);
-        char* k_out = static_cast<char*>(alt_keys);
-        char* v_in = static_cast<char*>(values);
-        char* v_out = static_cast<char*>(alt_values);
-        {
-            const uint64_t span = (uint64_t)begin[ns] - begin[0];
-            uint64_t grid = div_up(span, 1ull << 16);
-            if (grid > (uint64_t)ds->sm_count) grid = ds->sm_count;
-            if (grid == 0) grid = 1;
-            CUDA_TRY(s->table->seg_histogram(k_in, d_table, (uint32_t)start_bits, passes, d_hist, d_base, (int)ns, (int)grid, stream),
-                     "seg_histogram_kernel launch");
-            g_launches += 2;
-        }
-        for (int p = 0; p < passes; ++p) {
-            OnesweepArgs a;
-            a.keys_in = k_in;
-            a.keys_out = k_out;
-            a.vals_in = pairs ? v_in : nullptr;
-            a.vals_out = pairs ? v_out : nullptr;
-            a.n = begin[ns];
-            a.bit = (uint32_t)(start_bits + 8 * p);
-            a.status = d_pass + (uint64_t)p * pass_words;
-            a.gsum = a.status + vtiles * RADIX;
-            a.gprefix = a.gsum + vgroups * RADIX;
-            a.ticket = d_ticket + p;
-            a.sm_count = ds->sm_count;
-            a.base_in = d_base + (uint64_t)p * ns * RADIX;
-            a.base_out = nullptr;
-            a.pdl = false;
-            a.seg_table = d_table;
-            a.seg_vtiles = (uint32_t)vtiles;
-            CUDA_TRY(s->table->onesweep_seg[fast][vslot](a, stream), "onesweep_kernel (segmented) launch");
-            ++g_launches;
-            char* t = k_in; k_in = k_out; k_out = t;
-            t = v_in; v_in = v_out; v_out = t;
-        }
+        rc = sort_buckets_batch(s, *ds, fast, pairs, static_cast<char*>(keys), static_cast<char*>(values), static_cast<char*>(alt_keys),
+                                static_cast<char*>(alt_values), scratch, scratch_bytes, seg_begin + first_seg, identity, ns,
+                                seg_begin + first_seg, ns, start_bits, passes, stream);
+        if (rc) return rc;
         if ((passes & 1) && nseg > (uint32_t)MAX_SEGMENTS) {
             // several batches share the buffers: bring this batch's range home so that all results lie in one place
-            const uint64_t off = begin[0], cnt = (uint64_t)begin[ns] - begin[0];
-            CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(keys) + off * s->kbytes, static_cast<char*>(alt_keys) + off * s->kbytes,
-                                     cnt * s->kbytes, cudaMemcpyDeviceToDevice, stream), "copy-back keys");
-            if (pairs)
-                CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(values) + off * s->vbytes, static_cast<char*>(alt_values) + off * s->vbytes,
-                                         cnt * s->vbytes, cudaMemcpyDeviceToDevice, stream), "copy-back values");
+            const uint64_t off = seg_begin[first_seg], cnt = seg_begin[first_seg + ns] - off;
+            if (cnt) {
+                CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(keys) + off * s->kbytes, static_cast<char*>(alt_keys) + off * s->kbytes,
+                                         cnt * s->kbytes, cudaMemcpyDeviceToDevice, stream), "copy-back keys");
+                if (pairs)
+                    CUDA_TRY(cudaMemcpyAsync(static_cast<char*>(values) + off * s->vbytes, static_cast<char*>(alt_values) + off * s->vbytes,
+                                             cnt * s->vbytes, cudaMemcpyDeviceToDevice, stream), "copy-back values");
+            }
         }
     }
     if (result_in_alt) *result_in_alt = ((passes & 1) && nseg <= (uint32_t)MAX_SEGMENTS) ? 1 : 0;
+    return THRS_OK;
+}
+
+int thrs_sort_buckets_ex(thrs_sorter* s, void* keys, void* values, void* alt_keys, void* alt_values, void* scratch,
+                         uint64_t scratch_bytes, const uint64_t* chunk_begin, const uint32_t* chunk_bucket, uint32_t nchunk,
+                         const uint64_t* bucket_begin, uint32_t nbucket, int start_bits, int end_bits, void* stream_,
+                         int* result_in_alt)
+{
+    g_launches = 0;
+    if (result_in_alt) *result_in_alt = 0;
+    if (!s || !chunk_begin || !chunk_bucket || !bucket_begin) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: NULL argument");
+    if (nchunk > (uint32_t)MAX_SEGMENTS || nbucket > (uint32_t)MAX_SEGMENTS)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: at most 256 chunks and 256 buckets per call");
+    if (nchunk == 0 || nbucket == 0) return THRS_OK;
+    // the chunks of every bucket must add up to the bucket, and both layouts must cover the same extent
+    std::vector<uint64_t> sum(nbucket, 0);
+    for (uint32_t i = 0; i < nchunk; ++i) {
+        if (chunk_begin[i + 1] < chunk_begin[i]) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: chunk_begin must ascend");
+        if (chunk_bucket[i] >= nbucket) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: chunk_bucket out of range");
+        sum[chunk_bucket[i]] += chunk_begin[i + 1] - chunk_begin[i];
+    }
+    for (uint32_t b = 0; b < nbucket; ++b) {
+        if (bucket_begin[b + 1] < bucket_begin[b] || bucket_begin[b + 1] - bucket_begin[b] != sum[b])
+            return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: a bucket must be as large as its chunks together");
+        if (sum[b] > (uint64_t)VALUE_MASK) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: a bucket must stay below 2^30 items");
+    }
+    if (chunk_begin[0] != bucket_begin[0] || chunk_begin[nchunk] != bucket_begin[nbucket])
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: chunks and buckets must cover the same range");
+    if (chunk_begin[nchunk] > 0xffffffffull) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_buckets: offsets must stay below 2^32");
+    if (chunk_begin[nchunk] == chunk_begin[0]) return THRS_OK;
+    int passes = 0;
+    int rc = check_buckets_call(s, keys, values, alt_keys, alt_values, scratch, start_bits, end_bits, &passes);
+    if (rc) return rc;
+    if (passes == 0) return fail(THRS_ERR_BIT_RANGE, "thrs_sort_buckets: at least one pass (it is pass 0 that gathers the chunks)");
+    const DeviceState* ds = nullptr;
+    if ((rc = prepare_device(s, &ds))) return rc;
+    rc = sort_buckets_batch(s, *ds, resolve_fast(s, *ds), values != nullptr, static_cast<char*>(keys), static_cast<char*>(values),
+                            static_cast<char*>(alt_keys), static_cast<char*>(alt_values), scratch, scratch_bytes, chunk_begin,
+                            chunk_bucket, nchunk, bucket_begin, nbucket, start_bits, passes, static_cast<cudaStream_t>(stream_));
+    if (rc) return rc;
+    if (result_in_alt) *result_in_alt = passes & 1;
     return THRS_OK;
 }
 

@@ -7,15 +7,19 @@
 //   begin   top-digit histogram of the rank's slice + ONE stable out-of-place pass on the top digit
 //           (thrs_partition_pairs: this IS the last radix pass of the sort) into the send buffers;
 //           meanwhile a side stream pushes the 256 counts into every rank's window with the copy
-//           engines (no NCCL, no SMs) and reads the gathered table back to the host
-//   finish  splitters on digit boundaries (equal keys never straddle ranks); every (digit, source) chunk
-//           is copied by the copy engines straight into the owner's receive buffer, laid out
-//           DIGIT-MAJOR / SOURCE-MINOR, so that what a rank receives is already partitioned by the top
-//           digit with ties in global input order; chunks travel group by group (a group = a few
-//           consecutive digits of one owner), each followed by a 4-byte flag copy on the same stream;
-//           the owner's stream waits for a group's flags with cuStreamWaitValue32 (no spinning SM) and
-//           runs a SEGMENTED sort (thrs_sort_segments_ex, one segment per digit) on the remaining low
-//           bits of that group while the later groups are still in flight.
+//           engines (no NCCL, no SMs)
+//   plan    the gathered table comes back to the host; splitters on digit boundaries (equal keys never
+//           straddle ranks); every owner's digits are cut into a few GROUPS of consecutive digits
+//   send    per (destination, group) ONE contiguous copy of keys and one of values (the send buffers are
+//           digit-ordered, a group's digits are adjacent) by the copy engines straight into the owner's
+//           window, followed by a 4-byte flag copy on the same stream.  The owner's window is laid out
+//           group-major / SOURCE-major / digit-minor: a group is world chunks, each ordered by digit
+//   recv    the owner's stream waits for a group's flags with cuStreamWaitValue32 (no spinning SM) and
+//           sorts the group with thrs_sort_buckets_ex on the remaining low bits while later groups are
+//           still in flight: its pass 0 reads the (source, digit) chunks where they landed and writes
+//           digit-major buckets — the gather costs no extra pass — and the later passes run bucket by
+//           bucket.  Ties keep (source rank, position) order because a bucket's chunks are ranked in
+//           source order.
 // Concatenating the ranks' outputs is exactly std::stable_sort of the concatenated inputs.
 // Built from the public single-GPU entry points plus the CUDA runtime; flags are epoch numbers, so
 // nothing is ever reset between sorts.
@@ -114,7 +118,10 @@ struct thrs_xchg {
     int32_t owner[256] = {}, group[256] = {};
     uint64_t tot[256] = {}, recv[MAX_WORLD] = {};
     int phase = 0; // 0 idle, 1 begun, 2 planned (groups are being sent / received)
-    uint64_t send_base[257] = {}, land[256] = {}, my_counts[256] = {};
+    int32_t ngroups[MAX_WORLD] = {}; // groups of every owner
+    int max_groups = 0;
+    std::vector<uint64_t> counts;    // [world][256] of the sort in flight
+    uint64_t send_base[257] = {};
     int sent_groups = 0, recv_groups = 0, in_alt = 0;
 
     uint32_t* flag_ptr(char* win, int parity, int src, int slot) const
@@ -134,28 +141,6 @@ struct DeviceGuard {
     explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); }
     ~DeviceGuard() { int cur = 0; cudaGetDevice(&cur); if (cur != prev) cudaSetDevice(prev); }
 };
-
-// A group's bucket copies to one destination as ONE batched call (cudaMemcpyBatchAsync, CUDA 12.8+): 128 separate
-// cudaMemcpyAsync calls per destination cost the host several microseconds each — more than the copies take
-// on the wire at 8 GPUs — and the owner's sort cannot be enqueued before them.  Falls back to single copies.
-int copy_batch(std::vector<void*>& dsts, std::vector<void*>& srcs, std::vector<size_t>& sizes, cudaStream_t stream)
-{
-    if (dsts.empty()) return THRS_OK;
-    static int batch_ok = getenv("THRS_XCHG_NO_BATCH") ? 0 : 1;
-    if (batch_ok) {
-        cudaMemcpyAttributes attr;
-        memset(&attr, 0, sizeof(attr));
-        attr.srcAccessOrder = cudaMemcpySrcAccessOrderStream;
-        size_t idx = 0, fail = 0;
-        cudaError_t e = cudaMemcpyBatchAsync(dsts.data(), srcs.data(), sizes.data(), dsts.size(), &attr, &idx, 1, &fail, stream);
-        if (e == cudaSuccess) return THRS_OK;
-        cudaGetLastError();
-        batch_ok = 0; // not supported by this driver: single copies from now on
-    }
-    for (size_t i = 0; i < dsts.size(); ++i)
-        X_CUDA(cudaMemcpyAsync(dsts[i], srcs[i], sizes[i], cudaMemcpyDefault, stream), "bucket copy");
-    return THRS_OK;
-}
 
 double host_us()
 {
@@ -192,12 +177,12 @@ const char* thrs_xchg_last_error(void) { return g_x_err; }
 // Host-only planning, shared by every rank (all see the same table): owner of each top-digit bucket,
 // items every rank receives, and the group a bucket travels in.  counts[src * 256 + digit], 64-bit.
 int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner_of_digit, uint64_t* recv_totals,
-                   int32_t* group_of_digit)
+                   int32_t* group_of_digit, int32_t* groups_of_rank)
 {
     if (world < 1 || world > MAX_WORLD || !counts || !owner_of_digit || !recv_totals)
         return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_plan: bad argument");
     if (groups < 1) groups = 1;
-    if (groups > MAX_GROUPS) groups = MAX_GROUPS;
+    if (groups > MAX_GROUPS - MAX_WORLD) groups = MAX_GROUPS - MAX_WORLD;
     uint64_t tot[256], total = 0;
     for (int d = 0; d < 256; ++d) {
         tot[d] = 0;
@@ -215,15 +200,25 @@ int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner
         before += tot[d];
     }
     if (group_of_digit) {
-        // inside an owner: bucket -> group floor(groups * items_before_in_owner / owner_total), same rule
+        // inside an owner: bucket -> group floor(groups * items_before_in_owner / owner_total), the same rule, and a
+        // new group also whenever the current one holds 256 / world digits (a group is sorted as world chunks per
+        // digit in ONE segmented launch of at most 256 chunks).  At most groups + world groups per owner.
+        const int cap = 256 / world;
         uint64_t b = 0;
-        int cur = -1;
+        int cur = -1, gidx = 0, in_group = 0;
+        uint64_t last_rule = 0;
+        for (int r = 0; r < world; ++r)
+            if (groups_of_rank) groups_of_rank[r] = 0;
         for (int d = 0; d < 256; ++d) {
             const int o = owner_of_digit[d];
-            if (o != cur) { cur = o; b = 0; }
+            if (o != cur) { cur = o; b = 0; gidx = 0; in_group = 0; last_rule = 0; }
             uint64_t g = recv_totals[o] ? (uint64_t)((unsigned __int128)b * (uint64_t)groups / recv_totals[o]) : 0;
             if (g > (uint64_t)groups - 1) g = (uint64_t)groups - 1;
-            group_of_digit[d] = (int32_t)g;
+            if (in_group > 0 && (g != last_rule || in_group == cap)) { ++gidx; in_group = 0; }
+            last_rule = g;
+            group_of_digit[d] = gidx;
+            ++in_group;
+            if (groups_of_rank) groups_of_rank[o] = gidx + 1;
             b += tot[d];
         }
     }
@@ -271,7 +266,7 @@ int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_l
     x->cfg = *cfg;
     x->rank = rank;
     x->world = world;
-    x->groups = groups < 1 ? 1 : (groups > MAX_GROUPS ? MAX_GROUPS : groups);
+    x->groups = groups < 1 ? 1 : (groups > MAX_GROUPS - MAX_WORLD ? MAX_GROUPS - MAX_WORLD : groups);
     x->kbytes = (cfg->key_type == THRS_KEY_U32 || cfg->key_type == THRS_KEY_F32) ? 4 : 8;
     x->vbytes = cfg->value_type == THRS_VALUE_U32 ? 4 : 8;
     x->key_bits = x->kbytes * 8;
@@ -401,37 +396,27 @@ int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, 
     X_CUDA(cudaEventSynchronize(x->ev_host), "waiting for the gathered histograms");
     if (trace_on()) fprintf(stderr, "[xchg r%d] plan: waited %.0f us for the gathered counts\n", me, host_us() - t_sync0);
 
-    std::vector<uint64_t> counts((size_t)P * 256);
-    for (size_t i = 0; i < counts.size(); ++i) counts[i] = x->h_counts[i];
-    thrs_xchg_plan(P, x->groups, counts.data(), x->owner, x->recv, x->group);
+    x->counts.resize((size_t)P * 256);
+    for (size_t i = 0; i < x->counts.size(); ++i) x->counts[i] = x->h_counts[i];
+    const std::vector<uint64_t>& counts = x->counts;
+    thrs_xchg_plan(P, x->groups, counts.data(), x->owner, x->recv, x->group, x->ngroups);
+    x->max_groups = 0;
+    for (int r = 0; r < P; ++r) x->max_groups = x->ngroups[r] > x->max_groups ? x->ngroups[r] : x->max_groups;
     uint64_t need = 0;
     for (int r = 0; r < P; ++r) need = x->recv[r] > need ? x->recv[r] : need;
     if (needed_capacity) *needed_capacity = need;
-    if (groups) *groups = x->groups;
+    if (groups) *groups = x->max_groups;
     if (need > x->capacity) {
         // every rank sees the same table and takes the same decision: nobody copies anything
         X_CUDA(cudaStreamWaitEvent(stream, x->ev_part, 0), "cudaStreamWaitEvent");
         return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg: a rank's share exceeds the receive capacity (see needed_capacity)");
     }
-    // where my bucket d starts in my send buffers, and where my chunk of bucket d lands at its owner:
-    // digit-major / source-minor inside the owner's receive buffer
-    x->send_base[0] = 0;
+    x->send_base[0] = 0; // where my bucket d starts in my (digit-ordered) send buffers
     for (int d = 0; d < 256; ++d) {
-        x->my_counts[d] = counts[(size_t)me * 256 + d];
-        x->send_base[d + 1] = x->send_base[d] + x->my_counts[d];
-    }
-    uint64_t run = 0;
-    int cur = -1;
-    for (int d = 0; d < 256; ++d) {
-        if (x->owner[d] != cur) { cur = x->owner[d]; run = 0; }
-        uint64_t t = 0, mine = 0;
-        for (int s = 0; s < P; ++s) {
-            if (s == me) mine = run + t;
-            t += counts[(size_t)s * 256 + d];
-        }
-        x->land[d] = mine;
+        x->send_base[d + 1] = x->send_base[d] + counts[(size_t)me * 256 + d];
+        uint64_t t = 0;
+        for (int s = 0; s < P; ++s) t += counts[(size_t)s * 256 + d];
         x->tot[d] = t;
-        run += t;
     }
     for (int r = 0; r < P; ++r) {
         X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_part, 0), "cudaStreamWaitEvent");
@@ -444,85 +429,113 @@ int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, 
     return THRS_OK;
 }
 
-// outgoing buckets of the next group: keys and values on two streams per destination, then the group's flag
+// First and last+1 digit of group gi of owner r, and where that group starts in r's receive buffers.
+static bool group_range(const thrs_xchg* x, int r, int gi, int* d0, int* d1, uint64_t* start)
+{
+    uint64_t run = 0;
+    int a = -1, b = -1;
+    uint64_t st = 0;
+    for (int d = 0; d < 256; ++d) {
+        if (x->owner[d] != r) continue;
+        if (x->group[d] == gi) {
+            if (a < 0) { a = d; st = run; }
+            b = d + 1;
+        }
+        run += x->tot[d];
+    }
+    if (a < 0) return false;
+    *d0 = a; *d1 = b; *start = st;
+    return true;
+}
+
+// outgoing: the next group of every destination, ONE contiguous copy of keys and one of values each
+// (two streams per destination), then the group's flag
 int thrs_xchg_send_group(thrs_xchg* x)
 {
-    if (!x || x->phase != 2 || x->sent_groups >= x->groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send_group: out of sequence");
+    if (!x || x->phase != 2 || x->sent_groups >= x->max_groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_send_group: out of sequence");
     DeviceGuard g(x->device);
     const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank, gi = x->sent_groups;
     const double t0 = host_us();
-    std::vector<void*> dk, sk, dv, sv;
-    std::vector<size_t> zk, zv;
     for (int i = 1; i <= P; ++i) {
         const int r = (me + i) % P; // the own rank last: local copies are the cheapest to delay
-        dk.clear(); sk.clear(); dv.clear(); sv.clear(); zk.clear(); zv.clear();
-        for (int d = 0; d < 256; ++d) {
-            if (x->owner[d] != r || x->group[d] != gi) continue;
-            const uint64_t c = x->my_counts[d];
-            if (!c) continue;
-            dk.push_back(x->peer[r] + x->off_keys + x->land[d] * x->kbytes);
-            sk.push_back(x->send_keys + x->send_base[d] * x->kbytes);
-            zk.push_back(c * x->kbytes);
-            dv.push_back(x->peer[r] + x->off_vals + x->land[d] * x->vbytes);
-            sv.push_back(x->send_vals + x->send_base[d] * x->vbytes);
-            zv.push_back(c * x->vbytes);
-            if (r != me) x->last_sent_remote_bytes += c * (uint64_t)(x->kbytes + x->vbytes);
-            x->last_copies += 2;
+        if (gi >= x->ngroups[r]) continue;
+        int d0 = 0, d1 = 0;
+        uint64_t start = 0;
+        if (group_range(x, r, gi, &d0, &d1, &start)) {
+            // inside the group the owner keeps source-major order: my chunk follows those of the ranks before me
+            uint64_t before = 0, mine = 0;
+            for (int s = 0; s < P; ++s)
+                for (int d = d0; d < d1; ++d) {
+                    const uint64_t c = x->counts[(size_t)s * 256 + d];
+                    if (s < me) before += c;
+                    if (s == me) mine += c;
+                }
+            if (mine) {
+                const uint64_t dst = start + before, src = x->send_base[d0];
+                X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + dst * x->kbytes, x->send_keys + src * x->kbytes, mine * x->kbytes,
+                                       cudaMemcpyDeviceToDevice, x->copy[r]), "group copy (keys)");
+                X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_vals + dst * x->vbytes, x->send_vals + src * x->vbytes, mine * x->vbytes,
+                                       cudaMemcpyDeviceToDevice, x->copyv[r]), "group copy (values)");
+                X_CUDA(cudaEventRecord(x->ev_copyv[r], x->copyv[r]), "cudaEventRecord"); // the flag follows BOTH streams
+                X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_copyv[r], 0), "cudaStreamWaitEvent");
+                if (r != me) x->last_sent_remote_bytes += mine * (uint64_t)(x->kbytes + x->vbytes);
+                x->last_copies += 2;
+            }
         }
-        const bool any = !dk.empty();
-        int rc = copy_batch(dk, sk, zk, x->copy[r]);
-        if (rc == THRS_OK) rc = copy_batch(dv, sv, zv, x->copyv[r]);
-        if (rc) return rc;
-        if (any) { // the flag follows BOTH streams
-            X_CUDA(cudaEventRecord(x->ev_copyv[r], x->copyv[r]), "cudaEventRecord");
-            X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_copyv[r], 0), "cudaStreamWaitEvent");
-        }
-        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDefault, x->copy[r]), "group flag");
+        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDeviceToDevice, x->copy[r]), "group flag");
     }
     if (trace_on()) fprintf(stderr, "[xchg r%d] send_group %d: host %.0f us\n", me, gi, host_us() - t0);
     ++x->sent_groups;
-    if (x->sent_groups == x->groups)
+    if (x->sent_groups == x->max_groups)
         for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
     return THRS_OK;
 }
 
-// incoming buckets of the next group: wait for its flags on `stream`, then sort its buckets on the low bits
+// incoming: wait for the next group's flags on `stream`, then sort the group: pass 0 gathers its
+// (source, digit) chunks into digit buckets, the later passes run bucket by bucket
 int thrs_xchg_recv_group(thrs_xchg* x, void* stream_)
 {
     if (!x || x->phase != 2 || x->recv_groups >= x->sent_groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_recv_group: out of sequence");
     DeviceGuard g(x->device);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    const int par = (int)(x->epoch & 1u), me = x->rank, gi = x->recv_groups;
+    const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank, gi = x->recv_groups;
     ++x->recv_groups;
-    uint64_t seg_begin[257];
-    uint32_t nseg = 0;
-    uint64_t run = 0;
-    bool started = false;
-    for (int d = 0; d < 256; ++d) {
-        if (x->owner[d] != me) continue;
-        if (x->group[d] == gi) {
-            if (!started) { seg_begin[0] = run; started = true; }
-            seg_begin[++nseg] = run + x->tot[d];
-        }
-        run += x->tot[d];
-    }
+    if (gi >= x->ngroups[me]) return THRS_OK;
     const double t0 = host_us();
     int rc = wait_flags(x, stream, par, gi);
     if (rc) return rc;
-    if (!nseg || seg_begin[nseg] == seg_begin[0]) return THRS_OK;
+    int d0 = 0, d1 = 0;
+    uint64_t start = 0;
+    if (!group_range(x, me, gi, &d0, &d1, &start)) return THRS_OK;
+    const uint32_t nb = (uint32_t)(d1 - d0), nc = nb * (uint32_t)P;
+    uint64_t chunk_begin[257], bucket_begin[257];
+    uint32_t chunk_bucket[256];
+    uint64_t run = start;
+    for (int s = 0; s < P; ++s)
+        for (int d = d0; d < d1; ++d) {
+            const uint32_t i = (uint32_t)s * nb + (uint32_t)(d - d0);
+            chunk_begin[i] = run;
+            chunk_bucket[i] = (uint32_t)(d - d0);
+            run += x->counts[(size_t)s * 256 + d];
+        }
+    chunk_begin[nc] = run;
+    run = start;
+    for (int d = d0; d < d1; ++d) { bucket_begin[d - d0] = run; run += x->tot[d]; }
+    bucket_begin[nb] = run;
+    if (run == start) return THRS_OK;
     int ia = 0;
-    X_THRS(thrs_sort_segments_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals,
-                                 x->seg_scratch, x->seg_scratch_bytes, seg_begin, nseg, 0, x->key_bits - 8, stream, &ia));
-    if (trace_on()) fprintf(stderr, "[xchg r%d] recv_group %d: host %.0f us (%u buckets)\n", me, gi, host_us() - t0, nseg);
+    X_THRS(thrs_sort_buckets_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals, x->seg_scratch,
+                                x->seg_scratch_bytes, chunk_begin, chunk_bucket, nc, bucket_begin, nb, 0, x->key_bits - 8, stream, &ia));
     x->last_launches += (uint32_t)thrs_last_launch_count();
     x->in_alt = ia;
+    if (trace_on()) fprintf(stderr, "[xchg r%d] recv_group %d: host %.0f us (%u buckets, %u chunks)\n", me, gi, host_us() - t0, nb, nc);
     return THRS_OK;
 }
 
 int thrs_xchg_result(thrs_xchg* x, void* stream_, void** out_keys, void** out_values, uint64_t* out_count)
 {
     if (!x || !out_keys || !out_values || !out_count) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_result: NULL argument");
-    if (x->phase != 2 || x->recv_groups != x->groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_result: groups outstanding");
+    if (x->phase != 2 || x->recv_groups != x->max_groups) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_result: groups outstanding");
     x->phase = 0;
     x->began = false;
     DeviceGuard g(x->device);

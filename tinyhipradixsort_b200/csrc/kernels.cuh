@@ -456,16 +456,35 @@ seg_histogram_kernel(const KeyT* __restrict__ keys, const uint32_t* __restrict__
     }
 }
 
-// one block per (segment, pass): base[pass][seg][d] = begin[seg] + exclusive scan over d of hist[seg][pass][*]
+// Bin bases of a segmented sort whose pass 0 GATHERS: the input of pass 0 is a list of chunks (table A),
+// each belonging to an output bucket (map[chunk]); the chunks of a bucket keep their index order.  One
+// block per (bucket, pass), thread = bin:
+//   pass 0: base0[chunk][bin] = bucket begin + exclusive scan over bins of the bucket's total histogram
+//           + items with that bin in the bucket's EARLIER chunks        (one row per chunk: pass 0 runs chunk by chunk)
+//   pass p: base[p-1][bucket][bin] = bucket begin + exclusive scan over bins of the bucket's histogram of pass p
+// With one chunk per bucket (identity map) this is the plain segmented sort.
 static __global__ void __launch_bounds__(RADIX)
-seg_base_kernel(const uint32_t* __restrict__ hist, const uint32_t* __restrict__ seg_table, int passes, uint32_t* __restrict__ base)
+seg_base_kernel(const uint32_t* __restrict__ hist, const uint32_t* __restrict__ table_a, const uint32_t* __restrict__ table_b,
+                const uint32_t* __restrict__ map, int passes, uint32_t* __restrict__ base0, uint32_t* __restrict__ base_p)
 {
     __shared__ uint32_t s_scan[8];
-    const uint32_t nseg = seg_table[0];
-    const uint32_t seg = blockIdx.x / passes, p = blockIdx.x % passes;
-    const uint32_t c = hist[((size_t)seg * passes + p) * RADIX + threadIdx.x];
-    const uint32_t ex = block_exclusive_scan_256(c, s_scan, nullptr);
-    base[((size_t)p * nseg + seg) * RADIX + threadIdx.x] = seg_table[SEG_HEADER + (MAX_SEGMENTS + 1) + seg] + ex;
+    const uint32_t nchunk = table_a[0], nbucket = table_b[0];
+    const uint32_t bucket = blockIdx.x / passes, p = blockIdx.x % passes;
+    const uint32_t d = threadIdx.x;
+    uint32_t c = 0;
+    for (uint32_t i = 0; i < nchunk; ++i)
+        if (map[i] == bucket) c += hist[((size_t)i * passes + p) * RADIX + d];
+    const uint32_t ex = block_exclusive_scan_256(c, s_scan, nullptr) + table_b[SEG_HEADER + (MAX_SEGMENTS + 1) + bucket];
+    if (p == 0) {
+        uint32_t run = ex;
+        for (uint32_t i = 0; i < nchunk; ++i)
+            if (map[i] == bucket) {
+                base0[(size_t)i * RADIX + d] = run;
+                run += hist[((size_t)i * passes) * RADIX + d];
+            }
+    } else {
+        base_p[((size_t)(p - 1) * nbucket + bucket) * RADIX + d] = ex;
+    }
 }
 
 // ---------------------------------------------------------------------------------------

@@ -102,8 +102,9 @@ struct KernelTable {
     // segmented pass (several independent segments in one launch); same index meaning as onesweep
     cudaError_t (*onesweep_seg[2][4])(const OnesweepArgs& a, cudaStream_t stream);
     cudaError_t (*prepare_seg[2][4])();
-    cudaError_t (*seg_histogram)(const void* keys, const uint32_t* seg_table, uint32_t start_bit, int passes, uint32_t* hist,
-                                 uint32_t* base, int nseg, int grid, cudaStream_t stream);
+    cudaError_t (*seg_histogram)(const void* keys, const uint32_t* table_a, const uint32_t* table_b, const uint32_t* map,
+                                 uint32_t start_bit, int passes, uint32_t* hist, uint32_t* base0, uint32_t* base_p, int nbucket,
+                                 int grid, cudaStream_t stream);
     cudaError_t (*prepare_seg_histogram)();
     // one-block sort for n <= SMALL_SORT_MAX (small_sort.cuh)
     cudaError_t (*small[4])(void* keys, void* vals, uint32_t n, uint32_t start_bit, int passes, cudaStream_t stream);
@@ -198,8 +199,9 @@ cudaError_t launch_seg_histogram_p(const void* keys, const uint32_t* seg_table, 
     return cudaGetLastError();
 }
 template <class KeyT, int KIND, bool DESC>
-cudaError_t launch_seg_histogram(const void* keys, const uint32_t* seg_table, uint32_t start_bit, int passes, uint32_t* hist,
-                                 uint32_t* base, int nseg, int grid, cudaStream_t stream)
+cudaError_t launch_seg_histogram(const void* keys, const uint32_t* seg_table, const uint32_t* table_b, const uint32_t* map,
+                                 uint32_t start_bit, int passes, uint32_t* hist, uint32_t* base0, uint32_t* base_p, int nbucket,
+                                 int grid, cudaStream_t stream)
 {
     cudaError_t e = cudaErrorInvalidValue;
     switch (passes) {
@@ -219,7 +221,7 @@ cudaError_t launch_seg_histogram(const void* keys, const uint32_t* seg_table, ui
         }
     }
     if (e != cudaSuccess) return e;
-    seg_base_kernel<<<nseg * passes, RADIX, 0, stream>>>(hist, seg_table, passes, base);
+    seg_base_kernel<<<nbucket * passes, RADIX, 0, stream>>>(hist, seg_table, table_b, map, passes, base0, base_p);
     return cudaGetLastError();
 }
 template <class KeyT, int KIND, bool DESC, int PASSES>

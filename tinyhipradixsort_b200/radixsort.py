@@ -263,6 +263,21 @@ class RadixSort:
                                                int(startBits), int(endBits), _stream(stream), ctypes.byref(in_alt)))
         return bool(in_alt.value)
 
+    def sortBucketsOutOfPlace(self, keyBuffer, valueBuffer, altKeyBuffer, altValueBuffer, scratchBuffer, scratchBytes,
+                              chunkBegin, chunkBucket, bucketBegin, startBits, endBits, stream=None):
+        """thrs_sort_buckets_ex: pass 0 gathers the chunks (chunkBegin, chunkBucket) into the buckets
+        (bucketBegin); returns True if the sorted buckets lie in the alternates."""
+        cb = (ctypes.c_uint64 * len(chunkBegin))(*[int(x) for x in chunkBegin])
+        cm = (ctypes.c_uint32 * len(chunkBucket))(*[int(x) for x in chunkBucket])
+        bb = (ctypes.c_uint64 * len(bucketBegin))(*[int(x) for x in bucketBegin])
+        in_alt = ctypes.c_int(0)
+        _check(self._lib.thrs_sort_buckets_ex(self._h, _ptr(keyBuffer), None if valueBuffer is None else _ptr(valueBuffer),
+                                              _ptr(altKeyBuffer), None if altValueBuffer is None else _ptr(altValueBuffer),
+                                              _ptr(scratchBuffer), int(scratchBytes), cb, cm, len(chunkBucket), bb,
+                                              len(bucketBegin) - 1, int(startBits), int(endBits), _stream(stream),
+                                              ctypes.byref(in_alt)))
+        return bool(in_alt.value)
+
     # -- not in the reference: what unittest.cpp:399-414 does around a sort, in one C-ABI call
     def sortHost(self, host_keys, host_values, startBits, endBits):
         """Sort numpy arrays / CPU tensors in place (H2D, sort, D2H inside the call)."""
