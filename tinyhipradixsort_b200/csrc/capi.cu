@@ -825,11 +825,10 @@ static int sort_buckets_batch(thrs_sorter* s, const DeviceState& ds, int fast, b
     uint32_t* d_rowsP = d_rows0 + SegScratch::row_words(vtA);
     CUDA_TRY(cudaMemcpyAsync(d_tableA, host, 4ull * SegScratch::HEAD_WORDS, cudaMemcpyHostToDevice, stream), "upload segment tables");
     CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
-    // zero: tickets and histograms (bases are overwritten), then the status rows of all passes
-    CUDA_TRY(launch_zero(d_ticket, 4ull * (SegScratch::TICKET_WORDS + (uint64_t)nchunk * passes * RADIX), ds.sm_count, stream), "zero_kernel launch");
-    CUDA_TRY(launch_zero(d_rows0, 4ull * (SegScratch::row_words(vtA) + (uint64_t)(passes - 1) * SegScratch::row_words(vtB)), ds.sm_count, stream),
+    // zero, in one launch: tickets, histograms, (the bases in between, overwritten later anyway) and the status rows of all passes
+    CUDA_TRY(launch_zero(d_ticket, 4ull * (uint64_t)((d_rowsP + (uint64_t)(passes - 1) * SegScratch::row_words(vtB)) - d_ticket), ds.sm_count, stream),
              "zero_kernel launch");
-    g_launches += 2;
+    g_launches += 1;
     {
         const uint64_t span = chunk_begin[nchunk] - chunk_begin[0];
         uint64_t grid = div_up(span, 1ull << 16);
@@ -859,7 +858,9 @@ static int sort_buckets_batch(thrs_sorter* s, const DeviceState& ds, int fast, b
         a.sm_count = ds.sm_count;
         a.base_in = p == 0 ? d_base0 : d_baseP + (uint64_t)(p - 1) * nbucket * RADIX;
         a.base_out = nullptr;
-        a.pdl = false;
+        // pass p + 1 is launched programmatically dependent on pass p (its blocks take their places while p drains);
+        // pass 0 follows seg_base_kernel, which never triggers early, so it starts when that kernel has completed
+        a.pdl = s->pdl && p > 0;
         a.seg_table = p == 0 ? d_tableA : d_tableB;
         a.seg_vtiles = (uint32_t)vt;
         CUDA_TRY(s->table->onesweep_seg[fast][vslot](a, stream), "onesweep_kernel (segmented) launch");

@@ -36,7 +36,7 @@ struct Dev {
 struct thrs_mg {
     thrs_config cfg;
     int kbytes = 4, vbytes = 4;
-    int groups = 4;
+    int groups = 3;
     uint64_t max_local = 0, capacity = 0; // sizes the exchange contexts were built for
     std::vector<Dev> dev;
 };

@@ -48,7 +48,9 @@ int x_fail(int code, const char* what, cudaError_t e = cudaSuccess)
 
 constexpr int MAX_WORLD = 8;
 constexpr int MAX_GROUPS = 16;
-constexpr int FLAG_SLOTS = MAX_GROUPS + 1; // [MAX_GROUPS] = "counts have landed"
+// per source: [group] = "the group has landed", last = "counts have landed"
+constexpr int FLAG_SLOTS = MAX_GROUPS + 1;
+constexpr int COUNTS_SLOT = MAX_GROUPS;
 inline uint64_t up256(uint64_t x) { return (x + 255ull) & ~255ull; }
 
 // cuStreamWaitValue32 through the runtime's driver entry point (no link-time dependency on libcuda)
@@ -107,7 +109,8 @@ struct thrs_xchg {
     cudaStream_t side = nullptr;
     cudaStream_t copy[MAX_WORLD] = {};  // keys (and the group flags) to rank r
     cudaStream_t copyv[MAX_WORLD] = {}; // values to rank r, so that two copy engines work per destination
-    cudaEvent_t ev_counts = nullptr, ev_part = nullptr, ev_host = nullptr, ev_copy[MAX_WORLD] = {}, ev_copyv[MAX_WORLD] = {};
+    cudaEvent_t ev_counts = nullptr, ev_part = nullptr, ev_host = nullptr, ev_copy[MAX_WORLD] = {},
+                ev_copyv[MAX_WORLD][MAX_GROUPS] = {}; // one event per (destination, group): never re-recorded while a wait on it is pending
     uint32_t epoch = 0;
     uint64_t n_local = 0;
     bool began = false;
@@ -123,6 +126,9 @@ struct thrs_xchg {
     std::vector<uint64_t> counts;    // [world][256] of the sort in flight
     uint64_t send_base[257] = {};
     int sent_groups = 0, recv_groups = 0, in_alt = 0;
+    // THRS_XCHG_TRACE=1: device timeline of one sort (timing events; printed by thrs_xchg_result)
+    cudaEvent_t tr_part = nullptr, tr_sent[MAX_GROUPS] = {}, tr_wait[MAX_GROUPS] = {}, tr_sort[MAX_GROUPS] = {};
+    cudaEvent_t tr_begin = nullptr, tr_counts = nullptr, tr_copy_start = nullptr, tr_keys0 = nullptr;
 
     uint32_t* flag_ptr(char* win, int parity, int src, int slot) const
     {
@@ -200,10 +206,26 @@ int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner
         before += tot[d];
     }
     if (group_of_digit) {
-        // inside an owner: bucket -> group floor(groups * items_before_in_owner / owner_total), the same rule, and a
-        // new group also whenever the current one holds 256 / world digits (a group is sorted as world chunks per
-        // digit in ONE segmented launch of at most 256 chunks).  At most groups + world groups per owner.
+        // inside an owner: the groups GROW — group k ends where (k + 1)(k + 2) / (groups (groups + 1)) of the owner's
+        // items lie before (1/10, 3/10, 6/10, 1 for four groups): the first group is small so that the owner's sort
+        // starts early, the later ones arrive while the earlier ones are being sorted (copies are faster than the
+        // sort).  A new group also starts whenever the current one holds 256 / world digits (a group is sorted as
+        // world chunks per digit in ONE segmented launch of at most 256 chunks).  At most groups + world per owner.
         const int cap = 256 / world;
+        // THRS_XCHG_SPLITS="0.05,0.3,1" (dev tuning; identical on every rank): cumulative fractions instead of the rule above
+        double split[MAX_GROUPS];
+        int nsplit = 0;
+        if (const char* e = getenv("THRS_XCHG_SPLITS")) {
+            const char* q = e;
+            while (*q && nsplit < MAX_GROUPS - MAX_WORLD) {
+                char* end = nullptr;
+                const double v = strtod(q, &end);
+                if (end == q) break;
+                split[nsplit++] = v;
+                q = *end == ',' ? end + 1 : end;
+            }
+            if (nsplit > 0) groups = nsplit;
+        }
         uint64_t b = 0;
         int cur = -1, gidx = 0, in_group = 0;
         uint64_t last_rule = 0;
@@ -212,8 +234,15 @@ int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner
         for (int d = 0; d < 256; ++d) {
             const int o = owner_of_digit[d];
             if (o != cur) { cur = o; b = 0; gidx = 0; in_group = 0; last_rule = 0; }
-            uint64_t g = recv_totals[o] ? (uint64_t)((unsigned __int128)b * (uint64_t)groups / recv_totals[o]) : 0;
-            if (g > (uint64_t)groups - 1) g = (uint64_t)groups - 1;
+            uint64_t g = 0; // smallest k with b * groups * (groups + 1) < (k + 1)(k + 2) * owner_total
+            if (recv_totals[o]) {
+                if (nsplit > 0) { // dev override: cumulative fractions
+                    while (g + 1 < (uint64_t)groups && (double)b >= split[g] * (double)recv_totals[o]) ++g;
+                } else {
+                    const unsigned __int128 lhs = (unsigned __int128)b * (uint64_t)groups * (uint64_t)(groups + 1);
+                    while (g + 1 < (uint64_t)groups && lhs >= (unsigned __int128)((g + 1) * (g + 2)) * recv_totals[o]) ++g;
+                }
+            }
             if (in_group > 0 && (g != last_rule || in_group == cap)) { ++gidx; in_group = 0; }
             last_rule = g;
             group_of_digit[d] = gidx;
@@ -242,7 +271,8 @@ void thrs_xchg_destroy(thrs_xchg* x)
         if (x->copy[r]) cudaStreamDestroy(x->copy[r]);
         if (x->copyv[r]) cudaStreamDestroy(x->copyv[r]);
         if (x->ev_copy[r]) cudaEventDestroy(x->ev_copy[r]);
-        if (x->ev_copyv[r]) cudaEventDestroy(x->ev_copyv[r]);
+        for (int g2 = 0; g2 < MAX_GROUPS; ++g2)
+            if (x->ev_copyv[r][g2]) cudaEventDestroy(x->ev_copyv[r][g2]);
     }
     for (cudaEvent_t e : {x->ev_counts, x->ev_part, x->ev_host})
         if (e) cudaEventDestroy(e);
@@ -303,7 +333,7 @@ int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_l
             e = cudaStreamCreateWithFlags(&x->copy[r], cudaStreamNonBlocking);
             if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->copyv[r], cudaStreamNonBlocking);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_copy[r], cudaEventDisableTiming);
-            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_copyv[r], cudaEventDisableTiming);
+            for (int g2 = 0; g2 < MAX_GROUPS && e == cudaSuccess; ++g2) e = cudaEventCreateWithFlags(&x->ev_copyv[r][g2], cudaEventDisableTiming);
         }
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_counts, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_part, cudaEventDisableTiming);
@@ -343,6 +373,12 @@ int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t
         if (!x->peer[r]) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_begin: thrs_xchg_set_peers first");
     DeviceGuard g(x->device);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (trace_on() && !x->tr_part) {
+        cudaEventCreate(&x->tr_part); cudaEventCreate(&x->tr_begin); cudaEventCreate(&x->tr_counts);
+        cudaEventCreate(&x->tr_copy_start); cudaEventCreate(&x->tr_keys0);
+        for (int i = 0; i < MAX_GROUPS; ++i) { cudaEventCreate(&x->tr_sent[i]); cudaEventCreate(&x->tr_wait[i]); cudaEventCreate(&x->tr_sort[i]); }
+    }
+    if (trace_on()) cudaEventRecord(x->tr_begin, stream);
     ++x->epoch;
     const int par = (int)(x->epoch & 1u);
     x->n_local = n;
@@ -354,12 +390,13 @@ int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t
     x->last_launches = (uint32_t)thrs_last_launch_count();
     x->last_copies = 0;
     X_CUDA(cudaEventRecord(x->ev_part, stream), "cudaEventRecord");
+    if (trace_on()) cudaEventRecord(x->tr_part, stream);
     // side stream: push the counts to everyone (copy engines), then collect everyone's and bring them to the host
     X_CUDA(cudaStreamWaitEvent(x->side, x->ev_counts, 0), "cudaStreamWaitEvent");
     for (int i = 0; i < x->world; ++i) {
         const int r = (x->rank + i) % x->world;
         X_CUDA(cudaMemcpyAsync(x->counts_ptr(x->peer[r], par, x->rank), x->d_counts, 1024, cudaMemcpyDefault, x->side), "push counts");
-        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, x->rank, MAX_GROUPS), x->d_epoch + par, 4, cudaMemcpyDefault, x->side),
+        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, x->rank, COUNTS_SLOT), x->d_epoch + par, 4, cudaMemcpyDefault, x->side),
                "push counts flag");
     }
     // (the wait for everyone's counts is enqueued by thrs_xchg_plan_step: a context never enqueues a wait before
@@ -386,12 +423,13 @@ int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, 
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank;
     // everyone's counts -> host
-    int rc = wait_flags(x, x->side, par, MAX_GROUPS);
+    int rc = wait_flags(x, x->side, par, COUNTS_SLOT);
     if (rc) return rc;
     for (int s = 0; s < P; ++s)
         X_CUDA(cudaMemcpyAsync(x->h_counts + (size_t)s * 256, x->counts_ptr(x->window, par, s), 1024, cudaMemcpyDeviceToHost, x->side),
                "read counts");
     X_CUDA(cudaEventRecord(x->ev_host, x->side), "cudaEventRecord");
+    if (trace_on()) cudaEventRecord(x->tr_counts, x->side);
     const double t_sync0 = host_us();
     X_CUDA(cudaEventSynchronize(x->ev_host), "waiting for the gathered histograms");
     if (trace_on()) fprintf(stderr, "[xchg r%d] plan: waited %.0f us for the gathered counts\n", me, host_us() - t_sync0);
@@ -422,6 +460,8 @@ int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, 
         X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_part, 0), "cudaStreamWaitEvent");
         X_CUDA(cudaStreamWaitEvent(x->copyv[r], x->ev_part, 0), "cudaStreamWaitEvent");
     }
+    if (trace_on()) cudaEventRecord(x->tr_copy_start, x->copy[(me + 1) % P]);
+    (void)0;
     x->last_sent_remote_bytes = 0;
     x->sent_groups = x->recv_groups = 0;
     x->in_alt = 0;
@@ -470,24 +510,39 @@ int thrs_xchg_send_group(thrs_xchg* x)
                     if (s < me) before += c;
                     if (s == me) mine += c;
                 }
+            // ONE stream per destination.  Measured on 2 B200s (profiles/r2_exchange_timeline.txt): copies to one peer
+            // are served by one copy engine at ~475 GB/s whatever the number of streams — two streams to the same
+            // peer did not run side by side (alternating the groups over them: the second stream started when the
+            // first was empty; keys and values on different streams: the flag or event behind a group's values
+            // completed only after ALL queued value copies, i.e. at the very end of the exchange).
+            // THRS_XCHG_TWO_STREAMS=1 alternates the groups over two streams (the A/B kept for other boxes).
+            static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
+            cudaStream_t cs = (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
             if (mine) {
                 const uint64_t dst = start + before, src = x->send_base[d0];
                 X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + dst * x->kbytes, x->send_keys + src * x->kbytes, mine * x->kbytes,
-                                       cudaMemcpyDeviceToDevice, x->copy[r]), "group copy (keys)");
+                                       cudaMemcpyDeviceToDevice, cs), "group copy (keys)");
+                if (trace_on() && gi == 0 && i == 1) cudaEventRecord(x->tr_keys0, cs);
                 X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_vals + dst * x->vbytes, x->send_vals + src * x->vbytes, mine * x->vbytes,
-                                       cudaMemcpyDeviceToDevice, x->copyv[r]), "group copy (values)");
-                X_CUDA(cudaEventRecord(x->ev_copyv[r], x->copyv[r]), "cudaEventRecord"); // the flag follows BOTH streams
-                X_CUDA(cudaStreamWaitEvent(x->copy[r], x->ev_copyv[r], 0), "cudaStreamWaitEvent");
+                                       cudaMemcpyDeviceToDevice, cs), "group copy (values)");
                 if (r != me) x->last_sent_remote_bytes += mine * (uint64_t)(x->kbytes + x->vbytes);
                 x->last_copies += 2;
             }
         }
-        X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDeviceToDevice, x->copy[r]), "group flag");
+        {
+            static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
+            cudaStream_t cs = (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
+            X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDeviceToDevice, cs), "group flag");
+            if (trace_on() && i == 1) cudaEventRecord(x->tr_sent[gi], cs); // the next rank's group is out
+        }
     }
     if (trace_on()) fprintf(stderr, "[xchg r%d] send_group %d: host %.0f us\n", me, gi, host_us() - t0);
     ++x->sent_groups;
     if (x->sent_groups == x->max_groups)
-        for (int r = 0; r < P; ++r) X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
+        for (int r = 0; r < P; ++r) {
+            X_CUDA(cudaEventRecord(x->ev_copy[r], x->copy[r]), "cudaEventRecord");
+            X_CUDA(cudaEventRecord(x->ev_copyv[r][0], x->copyv[r]), "cudaEventRecord");
+        }
     return THRS_OK;
 }
 
@@ -504,6 +559,7 @@ int thrs_xchg_recv_group(thrs_xchg* x, void* stream_)
     const double t0 = host_us();
     int rc = wait_flags(x, stream, par, gi);
     if (rc) return rc;
+    if (trace_on()) { cudaEventRecord(x->tr_wait[gi], stream); cudaEventRecord(x->tr_sort[gi], stream); }
     int d0 = 0, d1 = 0;
     uint64_t start = 0;
     if (!group_range(x, me, gi, &d0, &d1, &start)) return THRS_OK;
@@ -528,6 +584,7 @@ int thrs_xchg_recv_group(thrs_xchg* x, void* stream_)
                                 x->seg_scratch_bytes, chunk_begin, chunk_bucket, nc, bucket_begin, nb, 0, x->key_bits - 8, stream, &ia));
     x->last_launches += (uint32_t)thrs_last_launch_count();
     x->in_alt = ia;
+    if (trace_on()) cudaEventRecord(x->tr_sort[gi], stream);
     if (trace_on()) fprintf(stderr, "[xchg r%d] recv_group %d: host %.0f us (%u buckets, %u chunks)\n", me, gi, host_us() - t0, nb, nc);
     return THRS_OK;
 }
@@ -541,7 +598,32 @@ int thrs_xchg_result(thrs_xchg* x, void* stream_, void** out_keys, void** out_va
     DeviceGuard g(x->device);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     // the send buffers may be overwritten by the next sort only after my own copies have left
-    for (int r = 0; r < x->world; ++r) X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
+    for (int r = 0; r < x->world; ++r) {
+        X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
+        X_CUDA(cudaStreamWaitEvent(stream, x->ev_copyv[r][0], 0), "cudaStreamWaitEvent");
+    }
+    if (trace_on() && x->tr_part) {
+        cudaStreamSynchronize(stream);
+        {
+            float a = -1, b = -1, c = -1, d = -1;
+            cudaEventElapsedTime(&a, x->tr_begin, x->tr_part);
+            cudaEventElapsedTime(&b, x->tr_begin, x->tr_counts);
+            cudaEventElapsedTime(&c, x->tr_part, x->tr_copy_start);
+            cudaEventElapsedTime(&d, x->tr_part, x->tr_keys0);
+            fprintf(stderr, "[xchg r%d] timeline: partition pass done %.3f ms after begin; gathered counts on the host side stream at %.3f; "
+                            "copy stream passes its wait %.3f ms after the pass; keys of group 0 to the next rank copied at %.3f\n",
+                    x->rank, a, b, c, d);
+        }
+        for (int gi = 0; gi < x->max_groups; ++gi) {
+            float a = -1, b = -1, c = -1;
+            cudaEventSynchronize(x->tr_sent[gi]);
+            cudaEventElapsedTime(&a, x->tr_part, x->tr_sent[gi]);
+            if (gi < x->ngroups[x->rank]) { cudaEventElapsedTime(&b, x->tr_part, x->tr_wait[gi]); cudaEventElapsedTime(&c, x->tr_part, x->tr_sort[gi]); }
+            fprintf(stderr, "[xchg r%d] timeline group %d (ms after my partition pass): my copies to the next rank done %.3f | incoming complete %.3f | sorted %.3f\n",
+                    x->rank, gi, a, b, c);
+        }
+        cudaGetLastError();
+    }
     *out_keys = x->in_alt ? x->alt_keys : x->window + x->off_keys;
     *out_values = x->in_alt ? x->alt_vals : x->window + x->off_vals;
     *out_count = x->recv[x->rank];

@@ -156,7 +156,7 @@ class CudaExchangeOps:
     pass the CUDA-IPC handles of the windows around; a sort itself involves no collective and no
     Python-side arithmetic (histogram exchange, splitters and copy lists are C++)."""
 
-    def __init__(self, key="u32", value_bytes=4, descending=False, groups=4):
+    def __init__(self, key="u32", value_bytes=4, descending=False, groups=3):
         import ctypes
 
         import torch
@@ -463,7 +463,7 @@ def bench(args, dist, rank, world, dev, g):
         ops = CudaLocalOps("u32", 4)
         ops.reserve(int(n_l * 1.05) + 4096)
     else:
-        ops = CudaExchangeOps("u32", 4, groups=int(os.environ.get("THRS_MG_GROUPS", "4")))
+        ops = CudaExchangeOps("u32", 4, groups=int(os.environ.get("THRS_MG_GROUPS", "3")))
     ds = DistributedRadixSort(dist, ops, "u32")
     keys, vals = torch.empty_like(keys0), torch.empty_like(vals0)
 
