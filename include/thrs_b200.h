@@ -345,6 +345,11 @@ THRS_API int thrs_cluster_sort_max(thrs_sorter* s, uint32_t* max_items);
 #define THRS_MID_SORT_MAX (1u << 20)
 THRS_API int thrs_set_mid_max(thrs_sorter* s, uint32_t max_items);
 
+/* Size the persistent grids of this sorter for at most `sms` multiprocessors (0 = all of them, the
+ * default).  The multi-GPU exchange uses it to keep a few SMs for its push kernel, which stores the
+ * outgoing buckets over NVLink while the received ones are being sorted. */
+THRS_API int thrs_set_sm_limit(thrs_sorter* s, int sms);
+
 /* Diagnostics. */
 THRS_API const char* thrs_last_error(void);        /* thread-local text of the last failure */
 THRS_API const char* thrs_version(void);

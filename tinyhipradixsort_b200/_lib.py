@@ -122,6 +122,7 @@ SIGNATURES = {
                                             ctypes.c_void_p, ctypes.c_uint32, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
                                             ctypes.POINTER(ctypes.c_int)]),
     "thrs_xchg_last_error": (ctypes.c_char_p, []),
+    "thrs_set_sm_limit": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_get_ranking_check": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_uint64)]),
 }
 

@@ -81,6 +81,7 @@ struct thrs_sorter {
     int force_multiblock = 0; // tests: run small inputs through the histogram + onesweep path too
     int cluster_path = 1;       // SMALL_SORT_MAX < n <= cluster_blocks x SMALL_SORT_MAX: one cluster launch
     int pdl = 1; // programmatic dependent launch between the launches of one sort (THRS_PDL=0 disables: dev A/B)
+    int sm_limit = 0; // thrs_set_sm_limit: persistent grids are sized for at most this many SMs (0 = all)
     int verify = 0; // THRS_VERIFY=1: every counter-return sort is repeated with the order-free ranking and compared
     uint32_t mid_max = THRS_MID_SORT_MAX; // n <= mid_max sorts with the quarter-size tile shape
     // workspace of thrs_sort_host (grown on demand, guarded)
@@ -105,6 +106,11 @@ struct thrs_sorter {
     int ev_parts = 0;
     bool ev_copyback = false;
 };
+
+static int effective_sms(const thrs_sorter* s, const DeviceState& ds)
+{
+    return (s->sm_limit > 0 && s->sm_limit < ds.sm_count) ? s->sm_limit : ds.sm_count;
+}
 
 static int resolve_fast(const thrs_sorter* s, const DeviceState& ds)
 {
@@ -488,7 +494,8 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
     // zero: histograms, bases, tickets, counters and the status rows of the passes we run
     const size_t clear_bytes = 4ull * (Scratch::CONTROL_WORDS + (uint64_t)passes * Scratch::pass_words(tiles_total));
     const bool pdl = s->pdl && !profiling && !(out && out->counts); // a copy sits between the histogram and the pass then
-    CUDA_TRY(launch_zero(temp, clear_bytes, ds.sm_count, stream), "zero_kernel launch");
+    const int sms = effective_sms(s, ds);
+    CUDA_TRY(launch_zero(temp, clear_bytes, sms, stream), "zero_kernel launch");
     ++g_launches;
     CUDA_TRY(mark(), "profile event");
 
@@ -496,7 +503,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
         const uint64_t vec_per_block = (uint64_t)HIST_THREADS * 4;
         const uint64_t nvec = (uint64_t)n * s->kbytes / 16;
         uint64_t grid = div_up(nvec > 0 ? nvec : 1, vec_per_block);
-        const uint64_t cap = (uint64_t)ds.sm_count; // one 1024-thread block (128 KiB table) per SM
+        const uint64_t cap = (uint64_t)sms; // one 1024-thread block (128 KiB table) per SM
         if (grid > cap) grid = cap;
         CUDA_TRY(s->table->histogram(keys, n, (uint32_t)start_bits, passes, sc, (int)grid, stream, pdl),
                  "histogram_kernel launch");
@@ -529,7 +536,7 @@ static int sort_core(thrs_sorter* s, const DeviceState& ds, int fast, void* keys
             a.gsum = sc.gsum(p, tiles_total) + group0 * RADIX;
             a.gprefix = sc.gprefix(p, tiles_total) + group0 * RADIX;
             a.ticket = sc.ticket(p, q);
-            a.sm_count = ds.sm_count;
+            a.sm_count = sms;
             a.base_in = sc.base(p, q);
             a.base_out = (q + 1 < parts) ? sc.base(p, q + 1) : nullptr;
             // the launch before this one on the stream is the histogram or a onesweep launch, unless
@@ -826,13 +833,14 @@ static int sort_buckets_batch(thrs_sorter* s, const DeviceState& ds, int fast, b
     CUDA_TRY(cudaMemcpyAsync(d_tableA, host, 4ull * SegScratch::HEAD_WORDS, cudaMemcpyHostToDevice, stream), "upload segment tables");
     CUDA_TRY(cudaEventRecord(table_ev, stream), "cudaEventRecord");
     // zero, in one launch: tickets, histograms, (the bases in between, overwritten later anyway) and the status rows of all passes
-    CUDA_TRY(launch_zero(d_ticket, 4ull * (uint64_t)((d_rowsP + (uint64_t)(passes - 1) * SegScratch::row_words(vtB)) - d_ticket), ds.sm_count, stream),
+    const int sms = effective_sms(s, ds);
+    CUDA_TRY(launch_zero(d_ticket, 4ull * (uint64_t)((d_rowsP + (uint64_t)(passes - 1) * SegScratch::row_words(vtB)) - d_ticket), sms, stream),
              "zero_kernel launch");
     g_launches += 1;
     {
         const uint64_t span = chunk_begin[nchunk] - chunk_begin[0];
         uint64_t grid = div_up(span, 1ull << 16);
-        if (grid > (uint64_t)ds.sm_count) grid = ds.sm_count;
+        if (grid > (uint64_t)sms) grid = sms;
         if (grid == 0) grid = 1;
         CUDA_TRY(s->table->seg_histogram(keys, d_tableA, d_tableB, d_map, (uint32_t)start_bits, passes, d_hist, d_base0, d_baseP,
                                          (int)nbucket, (int)grid, stream), "seg_histogram_kernel launch");
@@ -855,7 +863,7 @@ static int sort_buckets_batch(thrs_sorter* s, const DeviceState& ds, int fast, b
         a.gsum = a.status + vt * RADIX;
         a.gprefix = a.gsum + (vt / GROUP_TILES + 1) * RADIX;
         a.ticket = d_ticket + p;
-        a.sm_count = ds.sm_count;
+        a.sm_count = sms;
         a.base_in = p == 0 ? d_base0 : d_baseP + (uint64_t)(p - 1) * nbucket * RADIX;
         a.base_out = nullptr;
         // pass p + 1 is launched programmatically dependent on pass p (its blocks take their places while p drains);
@@ -1136,6 +1144,13 @@ int thrs_set_ranking(thrs_sorter* s, int ranking)
     if (ranking < THRS_RANKING_AUTO || ranking > THRS_RANKING_COUNTER_RETURN)
         return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_ranking: bad ranking");
     s->ranking_request = ranking;
+    return THRS_OK;
+}
+
+int thrs_set_sm_limit(thrs_sorter* s, int sms)
+{
+    if (!s || sms < 0) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_set_sm_limit: bad argument");
+    s->sm_limit = sms;
     return THRS_OK;
 }
 

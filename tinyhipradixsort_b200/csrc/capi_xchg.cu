@@ -74,6 +74,93 @@ WaitValue32Fn wait_value32()
     return fn;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// push_kernel — the outgoing side of the exchange done by a few SMs instead of the copy engines.
+// Measured on 8 B200s (profiles/r2_exchange_timeline.txt): all peer copies of one GPU share ~475 GB/s of
+// copy-engine throughput whatever the number of streams and destinations, which makes the exchange (7/8 of
+// the data at 8 GPUs) longer than the sort it is supposed to hide behind; plain SM stores into peer memory
+// reach 600-700 GB/s.  PUSH_BLOCKS blocks (one per SM: they ask for most of an SM's shared memory) walk
+// the job list group by group; a job is one contiguous run (a group's keys or values for one destination),
+// cut in 256 KiB pieces dealt round-robin to the blocks; 4-byte loads from the local send buffer (its phase
+// differs from the destination's), 16-byte stores to the peer.  When the last block is done with a group
+// it writes the group's flags (st.release.sys) into the destinations' windows.  The sort kernels of the
+// same GPU are sized for the remaining SMs (thrs_set_sm_limit).
+// ---------------------------------------------------------------------------------------------------
+struct PushJob {
+    const uint32_t* src;
+    uint32_t* dst;
+    uint64_t words; // 4-byte words
+};
+constexpr int PUSH_THREADS = 512;
+constexpr uint32_t PUSH_PIECE_WORDS = 64 * 1024; // 256 KiB
+constexpr int PUSH_MAX_JOBS = MAX_GROUPS * MAX_WORLD * 2;
+struct PushTable { // device copy, uploaded per sort
+    PushJob job[PUSH_MAX_JOBS];
+    uint32_t group_first_job[MAX_GROUPS + 1];
+    uint32_t* flag[MAX_GROUPS][MAX_WORLD]; // where to announce group g (null-terminated per group)
+    uint32_t groups;
+    uint32_t epoch;
+};
+
+__global__ void __launch_bounds__(PUSH_THREADS, 1) push_kernel(const PushTable* __restrict__ tab, uint32_t* __restrict__ done)
+{
+    extern __shared__ unsigned char push_smem[]; // only there to claim the SM
+    __shared__ uint32_t s_last;
+    const uint32_t groups = tab->groups;
+    for (uint32_t g = 0; g < groups; ++g) {
+        const uint32_t j0 = tab->group_first_job[g], j1 = tab->group_first_job[g + 1];
+        uint32_t piece0 = 0; // pieces of the jobs before j
+        for (uint32_t j = j0; j < j1; ++j) {
+            const uint64_t words = tab->job[j].words;
+            const uint32_t pieces = (uint32_t)((words + PUSH_PIECE_WORDS - 1) / PUSH_PIECE_WORDS);
+            // pieces piece0 .. piece0 + pieces - 1 of this group; mine are those congruent to blockIdx.x
+            uint32_t first = (blockIdx.x + gridDim.x - piece0 % gridDim.x) % gridDim.x;
+            for (uint32_t p = first; p < pieces; p += gridDim.x) {
+                const uint64_t w0 = (uint64_t)p * PUSH_PIECE_WORDS;
+                const uint32_t n = (uint32_t)(words - w0 < PUSH_PIECE_WORDS ? words - w0 : PUSH_PIECE_WORDS);
+                const uint32_t* src = tab->job[j].src + w0;
+                uint32_t* dst = tab->job[j].dst + w0;
+                uint32_t head = (uint32_t)(((16 - ((uintptr_t)dst & 15)) & 15) / 4);
+                if (head > n) head = n;
+                const uint32_t nvec = (n - head) / 4;
+                const uint32_t tail0 = head + nvec * 4;
+                if (threadIdx.x < head) dst[threadIdx.x] = src[threadIdx.x];
+                if (tail0 + threadIdx.x < n) dst[tail0 + threadIdx.x] = src[tail0 + threadIdx.x];
+                const uint32_t* sb = src + head;
+                uint4* db = reinterpret_cast<uint4*>(dst + head);
+                uint32_t i = threadIdx.x;
+                for (; i + 3 * PUSH_THREADS < nvec; i += 4 * PUSH_THREADS) {
+                    uint4 v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t* q = sb + 4ull * (i + u * PUSH_THREADS);
+                        v[u] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) db[i + u * PUSH_THREADS] = v[u];
+                }
+                for (; i < nvec; i += PUSH_THREADS) {
+                    const uint32_t* q = sb + 4ull * i;
+                    db[i] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+                }
+            }
+            piece0 += pieces;
+        }
+        // this block's share of group g is out; the last block announces the group to its destinations
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(&done[g], 1u) == gridDim.x - 1;
+        __syncthreads();
+        if (s_last) {
+            __threadfence_system();
+            if (threadIdx.x < MAX_WORLD) {
+                uint32_t* f = tab->flag[g][threadIdx.x];
+                if (f) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(tab->epoch) : "memory");
+            }
+        }
+    }
+}
+
 // fallback when stream memory operations are unavailable: one warp polls up to 32 flags
 __global__ void wait_flags_kernel(const volatile uint32_t* flags, int stride_words, int count, uint32_t epoch)
 {
@@ -121,6 +208,15 @@ struct thrs_xchg {
     int32_t owner[256] = {}, group[256] = {};
     uint64_t tot[256] = {}, recv[MAX_WORLD] = {};
     int phase = 0; // 0 idle, 1 begun, 2 planned (groups are being sent / received)
+    // SM push (see push_kernel): blocks to use (0 = copy engines only), device + pinned copies of the job table
+    int push_blocks = 0;
+    PushTable* d_push = nullptr;
+    PushTable* h_push = nullptr;
+    uint32_t* d_push_done = nullptr; // [2 parity][MAX_GROUPS]
+    cudaEvent_t ev_push_uploaded = nullptr, ev_push_done = nullptr;
+    cudaStream_t push = nullptr;
+    int sm_total = 0;
+    bool push_uploaded_once = false;
     int32_t ngroups[MAX_WORLD] = {}; // groups of every owner
     int max_groups = 0;
     std::vector<uint64_t> counts;    // [world][256] of the sort in flight
@@ -266,6 +362,12 @@ void thrs_xchg_destroy(thrs_xchg* x)
     if (x->d_epoch) cudaFree(x->d_epoch);
     if (x->h_epoch) cudaFreeHost(x->h_epoch);
     if (x->h_counts) cudaFreeHost(x->h_counts);
+    if (x->d_push) cudaFree(x->d_push);
+    if (x->h_push) cudaFreeHost(x->h_push);
+    if (x->d_push_done) cudaFree(x->d_push_done);
+    if (x->ev_push_uploaded) cudaEventDestroy(x->ev_push_uploaded);
+    if (x->ev_push_done) cudaEventDestroy(x->ev_push_done);
+    if (x->push) cudaStreamDestroy(x->push);
     if (x->side) cudaStreamDestroy(x->side);
     for (int r = 0; r < MAX_WORLD; ++r) {
         if (x->copy[r]) cudaStreamDestroy(x->copy[r]);
@@ -328,6 +430,23 @@ int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_l
         if (e == cudaSuccess) e = cudaMalloc(&x->d_epoch, 8);
         if (e == cudaSuccess) e = cudaMallocHost(&x->h_epoch, 8);
         if (e == cudaSuccess) e = cudaMallocHost(&x->h_counts, (size_t)world * 1024);
+        // Outgoing buckets: copy engines up to 2 ranks (475 GB/s hide behind the sort there), a push kernel on a few
+        // SMs beyond (THRS_XCHG_PUSH_SMS=n overrides, 0 = copy engines)
+        x->push_blocks = world > 2 ? 16 : 0;
+        if (const char* pe = getenv("THRS_XCHG_PUSH_SMS")) x->push_blocks = atoi(pe);
+        if (x->push_blocks < 0) x->push_blocks = 0;
+        if (x->push_blocks > 64) x->push_blocks = 64;
+        if (x->push_blocks > 0) {
+            if (e == cudaSuccess) e = cudaMalloc(&x->d_push, sizeof(PushTable));
+            if (e == cudaSuccess) e = cudaMallocHost(&x->h_push, sizeof(PushTable));
+            if (e == cudaSuccess) e = cudaMalloc(&x->d_push_done, 2 * MAX_GROUPS * 4);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_push_uploaded, cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&x->ev_push_done, cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->push, cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e == cudaSuccess) e = cudaDeviceGetAttribute(&x->sm_total, cudaDevAttrMultiProcessorCount, x->device);
+            if (e == cudaSuccess && x->sm_total <= x->push_blocks + 8) x->push_blocks = 0;
+        }
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&x->side, cudaStreamNonBlocking);
         for (int r = 0; r < world && e == cudaSuccess; ++r) {
             e = cudaStreamCreateWithFlags(&x->copy[r], cudaStreamNonBlocking);
@@ -385,6 +504,7 @@ int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t
     x->h_epoch[par] = x->epoch;
     X_CUDA(cudaMemcpyAsync(x->d_epoch + par, x->h_epoch + par, 4, cudaMemcpyHostToDevice, stream), "epoch upload");
     // top-digit histogram -> d_counts (ev_counts), then the stable pass on the top digit into the send buffers
+    thrs_set_sm_limit(x->sorter, 0); // nothing else runs yet: all SMs
     X_THRS(thrs_partition_pairs(x->sorter, keys, values, (uint32_t)n, x->part_temp, x->send_keys, x->send_vals, x->key_bits - 8,
                                 x->d_counts, x->ev_counts, stream));
     x->last_launches = (uint32_t)thrs_last_launch_count();
@@ -414,6 +534,8 @@ int thrs_xchg_begin(thrs_xchg* x, const void* keys, const void* values, uint64_t
 // and the segmented sort of group g.  By induction over the steps every wait is eventually satisfied.
 // One process per GPU: begin, plan, then send_group / recv_group alternating (thrs_xchg_finish).  One
 // process driving several ranks (thrs_mg_*): each step for ALL ranks before the next step.
+static bool group_range(const thrs_xchg* x, int r, int gi, int* d0, int* d1, uint64_t* start);
+
 int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, int* groups)
 {
     if (!x) return x_fail(THRS_ERR_INVALID_ARGUMENT, "thrs_xchg_plan_step: NULL context");
@@ -466,6 +588,55 @@ int thrs_xchg_plan_step(thrs_xchg* x, void* stream_, uint64_t* needed_capacity, 
     x->sent_groups = x->recv_groups = 0;
     x->in_alt = 0;
     x->phase = 2;
+    if (x->push_blocks > 0 && P > 1) {
+        // the whole outgoing side to OTHER ranks as one kernel on a few SMs (push_kernel); the sort launches of this
+        // step are sized for the remaining SMs
+        if (x->push_uploaded_once) X_CUDA(cudaEventSynchronize(x->ev_push_uploaded), "cudaEventSynchronize");
+        PushTable* t = x->h_push;
+        memset(t, 0, sizeof(*t));
+        uint32_t nj = 0;
+        for (int gi = 0; gi < x->max_groups; ++gi) {
+            t->group_first_job[gi] = nj;
+            int nf = 0;
+            for (int i = 1; i < P; ++i) {
+                const int r = (me + i) % P;
+                if (gi >= x->ngroups[r]) continue;
+                t->flag[gi][nf++] = x->flag_ptr(x->peer[r], par, me, gi);
+                int d0 = 0, d1 = 0;
+                uint64_t start = 0;
+                if (!group_range(x, r, gi, &d0, &d1, &start)) continue;
+                uint64_t before = 0, mine = 0;
+                for (int s = 0; s < P; ++s)
+                    for (int d = d0; d < d1; ++d) {
+                        const uint64_t c = counts[(size_t)s * 256 + d];
+                        if (s < me) before += c;
+                        if (s == me) mine += c;
+                    }
+                if (!mine) continue;
+                const uint64_t dst = start + before, src = x->send_base[d0];
+                t->job[nj++] = PushJob{reinterpret_cast<const uint32_t*>(x->send_keys + src * x->kbytes),
+                                       reinterpret_cast<uint32_t*>(x->peer[r] + x->off_keys + dst * x->kbytes), mine * x->kbytes / 4};
+                t->job[nj++] = PushJob{reinterpret_cast<const uint32_t*>(x->send_vals + src * x->vbytes),
+                                       reinterpret_cast<uint32_t*>(x->peer[r] + x->off_vals + dst * x->vbytes), mine * x->vbytes / 4};
+                x->last_sent_remote_bytes += mine * (uint64_t)(x->kbytes + x->vbytes);
+                x->last_copies += 2;
+            }
+        }
+        t->group_first_job[x->max_groups] = nj;
+        t->groups = (uint32_t)x->max_groups;
+        t->epoch = x->epoch;
+        X_CUDA(cudaStreamWaitEvent(x->push, x->ev_part, 0), "cudaStreamWaitEvent");
+        X_CUDA(cudaMemcpyAsync(x->d_push, t, sizeof(*t), cudaMemcpyHostToDevice, x->push), "upload push table");
+        X_CUDA(cudaEventRecord(x->ev_push_uploaded, x->push), "cudaEventRecord");
+        x->push_uploaded_once = true;
+        X_CUDA(cudaMemsetAsync(x->d_push_done + par * MAX_GROUPS, 0, MAX_GROUPS * 4, x->push), "cudaMemsetAsync");
+        push_kernel<<<x->push_blocks, PUSH_THREADS, 200 * 1024, x->push>>>(x->d_push, x->d_push_done + par * MAX_GROUPS);
+        X_CUDA(cudaGetLastError(), "push_kernel launch");
+        X_CUDA(cudaEventRecord(x->ev_push_done, x->push), "cudaEventRecord");
+        if (trace_on()) for (int gi = 0; gi < x->max_groups; ++gi) cudaEventRecord(x->tr_sent[gi], x->push);
+        ++x->last_launches;
+        thrs_set_sm_limit(x->sorter, x->sm_total - x->push_blocks);
+    }
     return THRS_OK;
 }
 
@@ -496,9 +667,11 @@ int thrs_xchg_send_group(thrs_xchg* x)
     DeviceGuard g(x->device);
     const int par = (int)(x->epoch & 1u), P = x->world, me = x->rank, gi = x->sent_groups;
     const double t0 = host_us();
+    const bool pushing = x->push_blocks > 0 && P > 1;
     for (int i = 1; i <= P; ++i) {
         const int r = (me + i) % P; // the own rank last: local copies are the cheapest to delay
         if (gi >= x->ngroups[r]) continue;
+        if (pushing && r != me) continue; // push_kernel sends and announces the remote part
         int d0 = 0, d1 = 0;
         uint64_t start = 0;
         if (group_range(x, r, gi, &d0, &d1, &start)) {
@@ -533,7 +706,7 @@ int thrs_xchg_send_group(thrs_xchg* x)
             static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
             cudaStream_t cs = (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
             X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDeviceToDevice, cs), "group flag");
-            if (trace_on() && i == 1) cudaEventRecord(x->tr_sent[gi], cs); // the next rank's group is out
+            if (trace_on() && i == 1 && !pushing) cudaEventRecord(x->tr_sent[gi], cs); // the next rank's group is out
         }
     }
     if (trace_on()) fprintf(stderr, "[xchg r%d] send_group %d: host %.0f us\n", me, gi, host_us() - t0);
@@ -602,6 +775,7 @@ int thrs_xchg_result(thrs_xchg* x, void* stream_, void** out_keys, void** out_va
         X_CUDA(cudaStreamWaitEvent(stream, x->ev_copy[r], 0), "cudaStreamWaitEvent");
         X_CUDA(cudaStreamWaitEvent(stream, x->ev_copyv[r][0], 0), "cudaStreamWaitEvent");
     }
+    if (x->push_blocks > 0 && x->world > 1) X_CUDA(cudaStreamWaitEvent(stream, x->ev_push_done, 0), "cudaStreamWaitEvent");
     if (trace_on() && x->tr_part) {
         cudaStreamSynchronize(stream);
         {
