@@ -81,7 +81,7 @@ WaitValue32Fn wait_value32()
 // the data at 8 GPUs) longer than the sort it is supposed to hide behind; plain SM stores into peer memory
 // reach 600-700 GB/s.  PUSH_BLOCKS blocks (one per SM: they ask for most of an SM's shared memory) walk
 // the job list group by group; a job is one contiguous run (a group's keys or values for one destination),
-// cut in 256 KiB pieces dealt round-robin to the blocks; 4-byte loads from the local send buffer (its phase
+// cut in 1 MiB pieces dealt round-robin to the blocks; 4-byte loads from the local send buffer (its phase
 // differs from the destination's), 16-byte stores to the peer.  When the last block is done with a group
 // it writes the group's flags (st.release.sys) into the destinations' windows.  The sort kernels of the
 // same GPU are sized for the remaining SMs (thrs_set_sm_limit).
@@ -91,8 +91,9 @@ struct PushJob {
     uint32_t* dst;
     uint64_t words; // 4-byte words
 };
-constexpr int PUSH_THREADS = 512;
-constexpr uint32_t PUSH_PIECE_WORDS = 64 * 1024; // 256 KiB
+constexpr int PUSH_THREADS = 1024;
+constexpr int PUSH_UNROLL = 8; // 16-byte stores in flight per thread: 128 KiB per SM (the loop is bound by the latency of its loads)
+constexpr uint32_t PUSH_PIECE_WORDS = 256 * 1024; // 1 MiB
 constexpr int PUSH_MAX_JOBS = MAX_GROUPS * MAX_WORLD * 2;
 struct PushTable { // device copy, uploaded per sort
     PushJob job[PUSH_MAX_JOBS];
@@ -129,19 +130,31 @@ __global__ void __launch_bounds__(PUSH_THREADS, 1) push_kernel(const PushTable* 
                 const uint32_t* sb = src + head;
                 uint4* db = reinterpret_cast<uint4*>(dst + head);
                 uint32_t i = threadIdx.x;
-                for (; i + 3 * PUSH_THREADS < nvec; i += 4 * PUSH_THREADS) {
-                    uint4 v[4];
+                if ((((uintptr_t)sb) & 15) == 0) { // source and destination share their 16-byte phase: vector loads
+                    const uint4* sv = reinterpret_cast<const uint4*>(sb);
+                    for (; i + (PUSH_UNROLL - 1) * PUSH_THREADS < nvec; i += PUSH_UNROLL * PUSH_THREADS) {
+                        uint4 v[PUSH_UNROLL];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const uint32_t* q = sb + 4ull * (i + u * PUSH_THREADS);
-                        v[u] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+                        for (int u = 0; u < PUSH_UNROLL; ++u) v[u] = __ldg(sv + i + u * PUSH_THREADS);
+#pragma unroll
+                        for (int u = 0; u < PUSH_UNROLL; ++u) db[i + u * PUSH_THREADS] = v[u];
                     }
+                    for (; i < nvec; i += PUSH_THREADS) db[i] = __ldg(sv + i);
+                } else {
+                    for (; i + (PUSH_UNROLL - 1) * PUSH_THREADS < nvec; i += PUSH_UNROLL * PUSH_THREADS) {
+                        uint4 v[PUSH_UNROLL];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) db[i + u * PUSH_THREADS] = v[u];
-                }
-                for (; i < nvec; i += PUSH_THREADS) {
-                    const uint32_t* q = sb + 4ull * i;
-                    db[i] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+                        for (int u = 0; u < PUSH_UNROLL; ++u) {
+                            const uint32_t* q = sb + 4ull * (i + u * PUSH_THREADS);
+                            v[u] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+                        }
+#pragma unroll
+                        for (int u = 0; u < PUSH_UNROLL; ++u) db[i + u * PUSH_THREADS] = v[u];
+                    }
+                    for (; i < nvec; i += PUSH_THREADS) {
+                        const uint32_t* q = sb + 4ull * i;
+                        db[i] = make_uint4(__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3));
+                    }
                 }
             }
             piece0 += pieces;
