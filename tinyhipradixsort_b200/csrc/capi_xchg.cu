@@ -76,10 +76,11 @@ WaitValue32Fn wait_value32()
 
 // ---------------------------------------------------------------------------------------------------
 // push_kernel — the outgoing side of the exchange done by a few SMs instead of the copy engines.
-// Measured on 8 B200s (profiles/r2_exchange_timeline.txt): all peer copies of one GPU share ~475 GB/s of
-// copy-engine throughput whatever the number of streams and destinations, which makes the exchange (7/8 of
-// the data at 8 GPUs) longer than the sort it is supposed to hide behind; plain SM stores into peer memory
-// reach 600-700 GB/s.  PUSH_BLOCKS blocks (one per SM: they ask for most of an SM's shared memory) walk
+// OPTIONAL (THRS_XCHG_PUSH_SMS=n; default off).  Measured on 2..8 B200s (profiles/r2_exchange_timeline.txt,
+// profiles/r2_microbench_copy_engine.txt): peer copies reach 762 GB/s per direction on an idle GPU but only
+// 350-475 GB/s while the same GPU runs a bandwidth-bound kernel, which makes the exchange (7/8 of the data at
+// 8 GPUs) longer than the sort it is supposed to hide behind.  This kernel was the attempt to add SM stores on
+// top: it reaches ~20 GB/s per SM (16 SMs: 330 GB/s), i.e. it costs the sort more SMs than it gains.  n blocks (one per SM: they ask for most of an SM's shared memory) walk
 // the job list group by group; a job is one contiguous run (a group's keys or values for one destination),
 // cut in 1 MiB pieces dealt round-robin to the blocks; 4-byte loads from the local send buffer (its phase
 // differs from the destination's), 16-byte stores to the peer.  When the last block is done with a group
@@ -443,9 +444,10 @@ int thrs_xchg_create(const thrs_config* cfg, int rank, int world, uint64_t max_l
         if (e == cudaSuccess) e = cudaMalloc(&x->d_epoch, 8);
         if (e == cudaSuccess) e = cudaMallocHost(&x->h_epoch, 8);
         if (e == cudaSuccess) e = cudaMallocHost(&x->h_counts, (size_t)world * 1024);
-        // Outgoing buckets: copy engines up to 2 ranks (475 GB/s hide behind the sort there), a push kernel on a few
-        // SMs beyond (THRS_XCHG_PUSH_SMS=n overrides, 0 = copy engines)
-        x->push_blocks = world > 2 ? 16 : 0;
+        // Outgoing buckets: copy engines.  THRS_XCHG_PUSH_SMS=n sends the remote part with push_kernel on n SMs instead
+        // (measured at 4 and 8 GPUs with 16 and 32 SMs: ~20 GB/s per SM, no faster overall than the copy engines,
+        // profiles/r2_exchange_timeline.txt — kept as a switch for other boxes)
+        x->push_blocks = 0;
         if (const char* pe = getenv("THRS_XCHG_PUSH_SMS")) x->push_blocks = atoi(pe);
         if (x->push_blocks < 0) x->push_blocks = 0;
         if (x->push_blocks > 64) x->push_blocks = 64;

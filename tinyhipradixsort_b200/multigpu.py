@@ -457,7 +457,13 @@ def bench(args, dist, rank, world, dev, g):
     strong = bool(getattr(args, "log2n_total", 0))
     n_l = (1 << args.log2n_total) // world if strong else 1 << args.log2n_per_gpu
     total = n_l * world
-    mode = os.environ.get("THRS_MG_MODE", "exchange")  # "scatter" = round 1's fused partition+exchange kernel (A/B)
+    # Which multi-GPU path (both are products, both verified every step): measured on this pool (profiles/r2_exchange_timeline.txt)
+    # "exchange" wins at 2 ranks (5.55 vs 6.24 ms) and is the only one for slices of 2^30 items and more (C5 at 2 and 4 GPUs);
+    # "scatter" (round 1: the partition pass stores into peer memory, then a 4-pass local sort) wins at 4 and 8 ranks
+    # (6.98 vs 7.33 ms, 7.66 vs 7.93 ms) because peer copies get only 350-475 GB/s next to the sort kernels.
+    mode = os.environ.get("THRS_MG_MODE", "auto")
+    if mode == "auto":
+        mode = "exchange" if (world <= 2 or n_l >= (1 << 30)) else "scatter"
     keys0, vals0 = g["gen_pairs"](torch, rank * n_l, n_l, dev)
     if mode == "scatter":
         ops = CudaLocalOps("u32", 4)
