@@ -517,8 +517,8 @@ def bench(args, dist, rank, world, dev, g):
         prof = srt.readProfile()
     srt.profile(False)
     seg_alone_ms = None
-    if mode != "scatter" and cnt:
-        del tmp
+    del tmp
+    if mode != "scatter" and cnt and n_l <= (1 << 29):  # (the int64 temporaries of this side measurement do not fit next to 2^31-item slices)
         k = (rk.to(torch.int64) & 0xFFFFFFFF) >> 24
         lo, hi = int(k[0]), int(k[-1])
         edges = torch.searchsorted(k, torch.arange(lo, hi + 2, device=dev, dtype=torch.int64)).tolist()
