@@ -112,6 +112,24 @@ THRS_API int thrs_sort_keys(thrs_sorter* s, void* keys, uint32_t n, void* temp,
 THRS_API int thrs_sort_pairs(thrs_sorter* s, void* keys, void* values, uint32_t n, void* temp,
                              int start_bits, int end_bits, void* stream);
 
+/* thrs_sort_keys for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The same kernels as thrs_sort_keys sort `keys` in place, stable, on
+ * bits [start_bits, end_bits), asynchronously on `stream`; what thrs_sort_keys takes as `temp` lives in a
+ * file-scope static __device__ array of THRS_NOALLOC_SCRATCH_BYTES (8 MiB) that every GPU which loads the
+ * library holds until exit.  The call allocates nothing: no cudaMalloc / cudaFree / allocating library
+ * routine, in any case.
+ * Limits: n <= THRS_NOALLOC_SCRATCH_BYTES / (2 * key bytes) — 1 048 576 four-byte or 524 288 eight-byte
+ * keys — else THRS_ERR_INVALID_ARGUMENT (use thrs_sort_keys with your own temp).  The sorter must have
+ * prepared the current device already (thrs_create with that device current, or one ordinary sort there):
+ * preparing allocates, so this call refuses instead (THRS_ERR_INVALID_ARGUMENT).  The first call per device
+ * looks the array's address up (cudaGetSymbolAddress); make it outside a capture — n = 0 is enough.
+ * ALL calls on one device share the array, in every sorter and thread of the process.  Each call clears the
+ * words it reads first, so the previous call's contents never matter, but two calls that OVERLAP on the GPU
+ * (different streams, or graphs launched concurrently) race on it: keep them on one stream or order them. */
+#define THRS_NOALLOC_SCRATCH_BYTES (8u << 20)
+THRS_API int thrs_sort_keys_noalloc(thrs_sorter* s, void* keys, uint32_t n, int start_bits, int end_bits, void* stream);
+
 /* Digit histogram of one 8-bit window: counts[d] = #keys whose digit
  * (getKeyBits(key) >> start_bit) & 0xFF is d, in sort order (descending sorters count
  * the complemented digit).  The same single-read kernel the sort starts with

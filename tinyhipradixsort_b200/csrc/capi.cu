@@ -1208,6 +1208,82 @@ int thrs_get_ranking_check(thrs_sorter* s, int* production_check_ok, uint64_t* i
     return THRS_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// thrs_sort_keys_noalloc: thrs_sort_keys for callers that cannot allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  Same launches (zero_kernel, histogram_kernel,
+// onesweep_kernel; one block / one cluster below 32 768 keys), but what thrs_sort_keys takes as `temp` —
+// tickets, digit histograms, look-back rows and the ping-pong key buffer — is g_noalloc_scratch below:
+// one static array per device that loads the library, held until exit;
+// the reference has no counterpart.  Nothing here (or in sort_core with profiling
+// off) calls cudaMalloc, cudaFree or an allocating library routine.
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: the address a
+// kernel can use comes from cudaGetSymbolAddress, taken once per device with that device current.
+// ---------------------------------------------------------------------------------------------------
+} // extern "C" (the array and its address table have internal linkage)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[THRS_NOALLOC_SCRATCH_BYTES];
+static int noalloc_scratch_of_current_device(int dev, void** out)
+{
+    static std::mutex mu;
+    static void* addr[MAX_DEVICES]; // device address of g_noalloc_scratch on device i (nullptr: not asked yet)
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_noalloc_scratch), "cudaGetSymbolAddress(static scratch)");
+        if (!p || ((uintptr_t)p % 256) != 0) return fail(THRS_ERR_CUDA, "cudaGetSymbolAddress(static scratch): unusable address");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return THRS_OK;
+}
+extern "C" {
+
+int thrs_sort_keys_noalloc(thrs_sorter* s, void* keys, uint32_t n, int start_bits, int end_bits, void* stream)
+{
+    g_launches = 0;
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_keys_noalloc: NULL sorter");
+    if (start_bits < 0 || end_bits < start_bits) return fail(THRS_ERR_BIT_RANGE, "sort: need 0 <= startBits <= endBits");
+    if (((end_bits - start_bits) % 8) != 0) return fail(THRS_ERR_BIT_RANGE, "sort: (endBits - startBits) must be a multiple of 8");
+    const uint64_t max_keys = THRS_NOALLOC_SCRATCH_BYTES / (2ull * s->kbytes);
+    if (n > max_keys)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_keys_noalloc: n exceeds the static scratch (%s keys at most); use thrs_sort_keys",
+                    s->kbytes == 4 ? "1 048 576" : "524 288");
+    // The device must have been prepared by thrs_create (or by an ordinary sort) while it was current:
+    // preparing runs the ranking checks, which allocate.  Only looked up here, never done.
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) {
+        cudaGetLastError();
+        return fail(THRS_ERR_NO_DEVICE, "no usable CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+    }
+    const DeviceState& ds = s->dev[dev];
+    {
+        std::lock_guard<std::mutex> lock(s->dev_mu);
+        if (!ds.prepared || ds.err != cudaSuccess)
+            return fail(THRS_ERR_INVALID_ARGUMENT,
+                        "thrs_sort_keys_noalloc: this sorter has not prepared the current device (thrs_create it with the device current)");
+    }
+    void* scratch = nullptr;
+    int rc = noalloc_scratch_of_current_device(dev, &scratch); // also for n == 0: the warm-up call
+    if (rc) return rc;
+    if (n == 0 || start_bits == end_bits) return THRS_OK;
+    if (!keys) return fail(THRS_ERR_INVALID_ARGUMENT, "sort: NULL buffer");
+    if (((uintptr_t)keys % s->kbytes) != 0) return fail(THRS_ERR_ALIGNMENT, "sort: misaligned buffer");
+    const int key_bits = s->kbytes * 8;
+    int passes = 0;
+    for (int b = start_bits; b < end_bits && b < key_bits; b += 8) ++passes;
+    if (passes == 0) return THRS_OK;
+    thrs_temp_def def;
+    thrs_temp_bytes(s, n, &def);
+    if (def.pSumBuffer + def.keyOutBuffer > THRS_NOALLOC_SCRATCH_BYTES)
+        return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_keys_noalloc: n exceeds the static scratch; use thrs_sort_keys");
+    // sort_core clears every scratch word this sort reads before it is read (zero_kernel heads the
+    // launches), so the previous call's contents do not matter; two calls that overlap on the GPU would
+    // share the array and race (thrs_b200.h).
+    return sort_core(s, ds, resolve_fast(s, ds), keys, nullptr, false, n, scratch, start_bits, passes,
+                     static_cast<cudaStream_t>(stream), false);
+}
+
 const char* thrs_version(void) { return "thrs_b200 0.1 (sm_100a onesweep)"; }
 int thrs_last_launch_count(void) { return g_launches; }
 
