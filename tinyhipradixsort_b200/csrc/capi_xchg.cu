@@ -704,8 +704,12 @@ int thrs_xchg_send_group(thrs_xchg* x)
             // first was empty; keys and values on different streams: the flag or event behind a group's values
             // completed only after ALL queued value copies, i.e. at the very end of the exchange).
             // THRS_XCHG_TWO_STREAMS=1 alternates the groups over two streams (the A/B kept for other boxes).
+            // THRS_XCHG_ONE_STREAM=1 (dev A/B): every copy of this rank on ONE stream, i.e. strictly in (group,
+            // destination) order — a single stream already reaches the idle copy rate, and with one stream per
+            // destination the engines pick among the queued copies of ALL groups in an order of their own.
             static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
-            cudaStream_t cs = (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
+            static const bool one = getenv("THRS_XCHG_ONE_STREAM") != nullptr;
+            cudaStream_t cs = one ? x->copy[me] : (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
             if (mine) {
                 const uint64_t dst = start + before, src = x->send_base[d0];
                 X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + dst * x->kbytes, x->send_keys + src * x->kbytes, mine * x->kbytes,
@@ -719,7 +723,8 @@ int thrs_xchg_send_group(thrs_xchg* x)
         }
         {
             static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
-            cudaStream_t cs = (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
+            static const bool one = getenv("THRS_XCHG_ONE_STREAM") != nullptr;
+            cudaStream_t cs = one ? x->copy[me] : (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
             X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDeviceToDevice, cs), "group flag");
             if (trace_on() && i == 1 && !pushing) cudaEventRecord(x->tr_sent[gi], cs); // the next rank's group is out
         }
