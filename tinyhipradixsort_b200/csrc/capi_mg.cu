@@ -56,7 +56,8 @@ static int build_contexts(thrs_mg* m, uint64_t max_local, uint64_t capacity)
     std::vector<void*> win(ndev, nullptr);
     for (int g = 0; g < ndev; ++g) {
         MG_CUDA(cudaSetDevice(m->dev[g].id), "cudaSetDevice");
-        MG_XCHG(thrs_xchg_create(&m->cfg, g, ndev, max_local, capacity, m->groups, &m->dev[g].x));
+        // pipeline depth: 3 growing groups at 2 ranks, 4 equal ones beyond (thrs_xchg_plan; profiles/r2_exchange_lanes.txt)
+        MG_XCHG(thrs_xchg_create(&m->cfg, g, ndev, max_local, capacity, ndev >= 3 ? 4 : m->groups, &m->dev[g].x));
         MG_XCHG(thrs_xchg_window(m->dev[g].x, &win[g], nullptr));
     }
     for (int g = 0; g < ndev; ++g) MG_XCHG(thrs_xchg_set_peers(m->dev[g].x, win.data()));

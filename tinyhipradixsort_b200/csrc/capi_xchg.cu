@@ -270,6 +270,19 @@ bool trace_on()
     return on != 0;
 }
 
+// number of ordered copy lanes for a world of P ranks (0 = one stream per destination): ONE lane from 3 ranks on —
+// every rank then sends to rank me + i at the same time, a permutation without two sources on one destination;
+// measured at 4 and 8 ranks, 2 to 4 lanes and one stream per destination are all slower (profiles/r2_exchange_lanes.txt).
+// THRS_XCHG_LANES overrides (read per call: a dev sweep changes it between sorts)
+int xchg_lanes(int P)
+{
+    int lanes = P >= 3 ? 1 : 0;
+    if (const char* e = getenv("THRS_XCHG_LANES")) lanes = atoi(e);
+    if (lanes < 0) lanes = 0;
+    if (lanes > P - 1) lanes = P - 1 > 0 ? P - 1 : 0;
+    return lanes;
+}
+
 int wait_flags(thrs_xchg* x, cudaStream_t stream, int parity, int slot)
 {
     if (WaitValue32Fn fn = wait_value32()) {
@@ -316,11 +329,15 @@ int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner
         before += tot[d];
     }
     if (group_of_digit) {
-        // inside an owner: the groups GROW — group k ends where (k + 1)(k + 2) / (groups (groups + 1)) of the owner's
-        // items lie before (1/10, 3/10, 6/10, 1 for four groups): the first group is small so that the owner's sort
-        // starts early, the later ones arrive while the earlier ones are being sorted (copies are faster than the
-        // sort).  A new group also starts whenever the current one holds 256 / world digits (a group is sorted as
-        // world chunks per digit in ONE segmented launch of at most 256 chunks).  At most groups + world per owner.
+        // inside an owner, at 2 ranks: the groups GROW — group k ends where (k + 1)(k + 2) / (groups (groups + 1)) of the
+        // owner's items lie before (1/10, 3/10, 6/10, 1 for four groups): the first group is small so that the owner's
+        // sort starts early, the later ones arrive while the earlier ones are being sorted (copies are faster than the
+        // sort).  At 3 ranks and more the copies are the slower side (most of the data crosses the link and the copy
+        // engines get half their idle rate next to the sort): EQUAL groups measured best there
+        // (profiles/r2_exchange_lanes.txt).  A new group also starts whenever the current one holds 256 / world digits
+        // (a group is sorted as world chunks per digit in ONE segmented launch of at most 256 chunks).  At most
+        // groups + world per owner.
+        const bool equal_groups = world >= 3;
         const int cap = 256 / world;
         // THRS_XCHG_SPLITS="0.05,0.3,1" (dev tuning; identical on every rank): cumulative fractions instead of the rule above
         double split[MAX_GROUPS];
@@ -348,6 +365,9 @@ int thrs_xchg_plan(int world, int groups, const uint64_t* counts, int32_t* owner
             if (recv_totals[o]) {
                 if (nsplit > 0) { // dev override: cumulative fractions
                     while (g + 1 < (uint64_t)groups && (double)b >= split[g] * (double)recv_totals[o]) ++g;
+                } else if (equal_groups) { // smallest k with b * groups < (k + 1) * owner_total
+                    const unsigned __int128 lhs = (unsigned __int128)b * (uint64_t)groups;
+                    while (g + 1 < (uint64_t)groups && lhs >= (unsigned __int128)(g + 1) * recv_totals[o]) ++g;
                 } else {
                     const unsigned __int128 lhs = (unsigned __int128)b * (uint64_t)groups * (uint64_t)(groups + 1);
                     while (g + 1 < (uint64_t)groups && lhs >= (unsigned __int128)((g + 1) * (g + 2)) * recv_totals[o]) ++g;
@@ -704,12 +724,16 @@ int thrs_xchg_send_group(thrs_xchg* x)
             // first was empty; keys and values on different streams: the flag or event behind a group's values
             // completed only after ALL queued value copies, i.e. at the very end of the exchange).
             // THRS_XCHG_TWO_STREAMS=1 alternates the groups over two streams (the A/B kept for other boxes).
-            // THRS_XCHG_ONE_STREAM=1 (dev A/B): every copy of this rank on ONE stream, i.e. strictly in (group,
-            // destination) order — a single stream already reaches the idle copy rate, and with one stream per
-            // destination the engines pick among the queued copies of ALL groups in an order of their own.
+            // THRS_XCHG_LANES=k: the remote copies of this rank run on k streams ("lanes"), the i-th destination after
+            // me on lane (i - 1) % k, every lane strictly in (group, destination) order; local copies keep their own
+            // stream.  0 = one stream per destination (the round-2 first version).  Measured at 8 ranks
+            // (profiles/r2_exchange_lanes.txt): with one stream per destination the copy engines pick among the
+            // queued copies of ALL groups in an order of their own and group 0 completes late; a few ordered lanes
+            // deliver the groups in order at the same aggregate rate.
             static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
-            static const bool one = getenv("THRS_XCHG_ONE_STREAM") != nullptr;
-            cudaStream_t cs = one ? x->copy[me] : (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
+            const int lanes = xchg_lanes(P);
+            cudaStream_t cs = (lanes > 0 && r != me) ? x->copy[(me + 1 + (i - 1) % lanes) % P]
+                                                     : (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
             if (mine) {
                 const uint64_t dst = start + before, src = x->send_base[d0];
                 X_CUDA(cudaMemcpyAsync(x->peer[r] + x->off_keys + dst * x->kbytes, x->send_keys + src * x->kbytes, mine * x->kbytes,
@@ -723,8 +747,9 @@ int thrs_xchg_send_group(thrs_xchg* x)
         }
         {
             static const bool two = getenv("THRS_XCHG_TWO_STREAMS") != nullptr;
-            static const bool one = getenv("THRS_XCHG_ONE_STREAM") != nullptr;
-            cudaStream_t cs = one ? x->copy[me] : (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
+            const int lanes = xchg_lanes(P);
+            cudaStream_t cs = (lanes > 0 && r != me) ? x->copy[(me + 1 + (i - 1) % lanes) % P]
+                                                     : (two && (gi & 1)) ? x->copyv[r] : x->copy[r];
             X_CUDA(cudaMemcpyAsync(x->flag_ptr(x->peer[r], par, me, gi), x->d_epoch + par, 4, cudaMemcpyDeviceToDevice, cs), "group flag");
             if (trace_on() && i == 1 && !pushing) cudaEventRecord(x->tr_sent[gi], cs); // the next rank's group is out
         }
@@ -772,6 +797,14 @@ int thrs_xchg_recv_group(thrs_xchg* x, void* stream_)
     for (int d = d0; d < d1; ++d) { bucket_begin[d - d0] = run; run += x->tot[d]; }
     bucket_begin[nb] = run;
     if (run == start) return THRS_OK;
+    // THRS_XCHG_SORT_SMS=k (dev A/B): size the segmented sort's grids for k SMs while later groups are still being
+    // copied (the copy engines get a smaller share of the memory system next to a kernel that fills every SM); the
+    // last group, with nothing left in flight towards this rank, uses all of them
+    if (!(x->push_blocks > 0 && P > 1))
+        if (const char* e = getenv("THRS_XCHG_SORT_SMS")) {
+            const int k = atoi(e);
+            thrs_set_sm_limit(x->sorter, (k > 0 && gi + 1 < x->ngroups[me]) ? k : 0);
+        }
     int ia = 0;
     X_THRS(thrs_sort_buckets_ex(x->sorter, x->window + x->off_keys, x->window + x->off_vals, x->alt_keys, x->alt_vals, x->seg_scratch,
                                 x->seg_scratch_bytes, chunk_begin, chunk_bucket, nc, bucket_begin, nb, 0, x->key_bits - 8, stream, &ia));

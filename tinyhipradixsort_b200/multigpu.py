@@ -457,19 +457,19 @@ def bench(args, dist, rank, world, dev, g):
     strong = bool(getattr(args, "log2n_total", 0))
     n_l = (1 << args.log2n_total) // world if strong else 1 << args.log2n_per_gpu
     total = n_l * world
-    # Which multi-GPU path (both are products, both verified every step): measured on this pool (profiles/r2_exchange_timeline.txt)
-    # "exchange" wins at 2 ranks (5.55 vs 6.24 ms) and is the only one for slices of 2^30 items and more (C5 at 2 and 4 GPUs);
-    # "scatter" (round 1: the partition pass stores into peer memory, then a 4-pass local sort) wins at 4 and 8 ranks
-    # (6.98 vs 7.33 ms, 7.66 vs 7.93 ms) because peer copies get only 350-475 GB/s next to the sort kernels.
+    # Which multi-GPU path (both are products, both verified every step).  Measured on this pool
+    # (profiles/r2_exchange_timeline.txt, profiles/r2_exchange_lanes.txt): the exchange path wins at every world size once
+    # its copies run on ONE ordered lane from 3 ranks on (2 ranks 5.55 vs 6.24 ms, 4 ranks 6.20 vs 6.99, 8 ranks 7.0 vs 7.7-7.9);
+    # THRS_MG_MODE=scatter selects the round-1 path (the partition pass stores into peer memory, then a 4-pass local sort).
     mode = os.environ.get("THRS_MG_MODE", "auto")
     if mode == "auto":
-        mode = "exchange" if (world <= 2 or n_l >= (1 << 30)) else "scatter"
+        mode = "exchange"
     keys0, vals0 = g["gen_pairs"](torch, rank * n_l, n_l, dev)
     if mode == "scatter":
         ops = CudaLocalOps("u32", 4)
         ops.reserve(int(n_l * 1.05) + 4096)
     else:
-        ops = CudaExchangeOps("u32", 4, groups=int(os.environ.get("THRS_MG_GROUPS", "3")))
+        ops = CudaExchangeOps("u32", 4, groups=int(os.environ.get("THRS_MG_GROUPS", "3" if world <= 2 else "4")))
     ds = DistributedRadixSort(dist, ops, "u32")
     keys, vals = torch.empty_like(keys0), torch.empty_like(vals0)
 
