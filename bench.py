@@ -7,8 +7,9 @@ libthrs_b200.so (thrs_sort_pairs: 1 histogram launch + 1 onesweep launch per 8-b
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 N = 1 : config C2 of BASELINE.json — 2^28 uniform-random u32 keys + u32 values, bits [0,32).
-N > 1 : the partitioned sort of config C5 (MSD splitters + all-to-all + local onesweep),
-        2^28 pairs per GPU by default (weak scaling; --log2n-per-gpu 29 at N=8 is 2^32 total).
+N > 1 : the partitioned sort of config C5 (top-digit pass = the sort's last radix pass, copy-engine bucket
+        exchange over NVLink, segmented 3-pass sort of the received buckets; no collective on the data path),
+        2^28 pairs per GPU by default (weak scaling); --log2n-total 32 is C5 as stated (2^32 pairs, strong).
 
 `value` is sorted keys/s with the input resident in HBM (CUDA events around the sort call
 only, input restored outside the timed region, inputs of 2 GiB are far larger than the
