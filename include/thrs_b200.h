@@ -145,6 +145,19 @@ THRS_API int thrs_digit_histogram(thrs_sorter* s, const void* keys, uint32_t n, 
 THRS_API int thrs_sort_host(thrs_sorter* s, void* host_keys, void* host_values, uint32_t n,
                             int start_bits, int end_bits);
 
+/* Streaming form of thrs_sort_host for hosts that sort batch after batch (no counterpart in the reference, whose
+ * caller would build the same thing from sortPairs on several streams, hpp:845-852): submit enqueues the upload,
+ * the sort and the download of one batch on three internal streams and returns at once; wait blocks until that
+ * batch is back, sorted, in the host buffers it came from.  THRS_HOST_SLOTS batches can be in flight: the
+ * upload of batch i+1 then overlaps the sort of batch i and the download of batch i-1 (PCIe is full duplex), so
+ * a stream of sorts costs one PCIe direction per batch instead of two.  Host buffers should be pinned (pageable
+ * memory makes the copies synchronous) and must stay untouched until wait returns.  A slot holds its own device
+ * workspace (grown on demand, freed by thrs_destroy); submitting to a slot that is in flight is an error. */
+#define THRS_HOST_SLOTS 4
+THRS_API int thrs_sort_host_submit(thrs_sorter* s, int slot, void* host_keys, void* host_values, uint32_t n,
+                                   int start_bits, int end_bits);
+THRS_API int thrs_sort_host_wait(thrs_sorter* s, int slot);
+
 /* Host getKeyBits family, fpKey.hpp:15-38 (ascending order function). */
 THRS_API uint32_t thrs_key_bits_u32(uint32_t x);
 THRS_API uint64_t thrs_key_bits_u64(uint64_t x);

@@ -142,3 +142,8 @@ def test_no_cpu_fallback_without_device():
     k = np.arange(10, dtype=np.uint32)
     with pytest.raises(thrs.ThrsError):
         s.sortHost(k, None, 0, 32)
+    with pytest.raises(thrs.ThrsError):
+        s.sortHostSubmit(0, k, None, 0, 32)
+    with pytest.raises(thrs.ThrsError):
+        s.sortHostWait(thrs.RadixSort.HOST_SLOTS)  # slot out of range is rejected without a device, too
+    s.sortHostWait(0)  # nothing in flight: returns

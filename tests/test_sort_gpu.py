@@ -309,6 +309,45 @@ def test_sort_host_entry_point():
     assert np.array_equal(k, oracle.sort("f32", keys)[0])
 
 
+def test_sort_host_streaming_slots():
+    """thrs_sort_host_submit / _wait: several batches in flight (upload, sort and download on three streams),
+    every batch back in its own pinned host arrays equals the oracle; slots are reusable; a busy slot refuses."""
+    import torch
+
+    sorter = make_sorter("u32", 4)
+    rng = oracle.SplitMix64(52)
+    slots = thrs.RadixSort.HOST_SLOTS
+    batches = []
+    for i, n in enumerate((300000, 5000, 1 << 20, 77777, 1, 40000, 1234567)):
+        keys = rng.randomize("u32", n, mode=1)
+        keys[::7] = keys[0]
+        vals = np.arange(n, dtype=np.uint32)
+        hk = torch.from_numpy(keys.view(np.int32).copy()).pin_memory()
+        hv = torch.from_numpy(vals.view(np.int32).copy()).pin_memory()
+        batches.append((keys, vals, hk, hv))
+    for i, (keys, vals, hk, hv) in enumerate(batches):
+        slot = i % slots
+        sorter.sortHostWait(slot)  # no-op for a free slot, else the batch submitted `slots` iterations ago
+        sorter.sortHostSubmit(slot, hk, hv, 0, 32)
+        if i == 1:
+            with pytest.raises(thrs.ThrsError):
+                sorter.sortHostSubmit(slot, hk, hv, 0, 32)  # still in flight
+    for slot in range(slots):
+        sorter.sortHostWait(slot)
+    for keys, vals, hk, hv in batches:
+        ek, ev = oracle.sort("u32", keys, vals)
+        assert np.array_equal(hk.numpy().view(np.uint32), ek) and np.array_equal(hv.numpy().view(np.uint32), ev)
+    # keys only, pageable numpy memory, the same slot twice
+    for n in (99999, 3):
+        keys = rng.randomize("u32", n, mode=1)
+        k = keys.copy()
+        sorter.sortHostSubmit(2, k, None, 8, 24)
+        sorter.sortHostWait(2)
+        assert np.array_equal(k, oracle.sort("u32", keys, None, 8, 24)[0])
+    with pytest.raises(thrs.ThrsError):
+        sorter.sortHostSubmit(slots, k, None, 0, 32)
+
+
 def test_misaligned_key_pointer_keys_not_16B_aligned():
     # keyIs16byteAligned=false callers (hpp:699-700): any element-aligned pointer works
     cfg = thrs.RadixSort.Config().configureWithKeyPair("u32", 4)

@@ -57,6 +57,9 @@ SIGNATURES = {
                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "thrs_sort_host": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
                                       ctypes.c_int, ctypes.c_int]),
+    "thrs_sort_host_submit": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32,
+                                             ctypes.c_int, ctypes.c_int]),
+    "thrs_sort_host_wait": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "thrs_key_bits_u32": (ctypes.c_uint32, [ctypes.c_uint32]),
     "thrs_key_bits_u64": (ctypes.c_uint64, [ctypes.c_uint64]),
     "thrs_key_bits_f32": (ctypes.c_uint32, [ctypes.c_uint32]),

@@ -91,6 +91,16 @@ struct thrs_sorter {
     void* ws_temp = nullptr;
     uint64_t ws_keys_bytes = 0, ws_vals_bytes = 0, ws_temp_bytes = 0;
     cudaStream_t ws_stream = nullptr;
+    // thrs_sort_host_submit / _wait: THRS_HOST_SLOTS independent workspaces and three streams (upload, sort,
+    // download), so that the upload of one sort overlaps the download of another (PCIe is full duplex)
+    struct HostSlot {
+        void *keys = nullptr, *vals = nullptr, *temp = nullptr;
+        uint64_t keys_bytes = 0, vals_bytes = 0, temp_bytes = 0;
+        cudaEvent_t up = nullptr, sorted = nullptr, down = nullptr;
+        bool busy = false;
+    };
+    HostSlot hslot[THRS_HOST_SLOTS];
+    cudaStream_t hs_up = nullptr, hs_sort = nullptr, hs_down = nullptr;
     // pinned staging ring for the segment tables of thrs_sort_segments_* (a pageable source would make
     // cudaMemcpyAsync wait for the stream first, and callers enqueue behind cross-GPU waits)
     static constexpr int SEG_RING = 64;
@@ -174,6 +184,16 @@ void thrs_destroy(thrs_sorter* s)
     if (s->ws_vals) cudaFree(s->ws_vals);
     if (s->ws_temp) cudaFree(s->ws_temp);
     if (s->ws_stream) cudaStreamDestroy(s->ws_stream);
+    for (auto& h : s->hslot) {
+        if (h.busy && h.down) cudaEventSynchronize(h.down);
+        if (h.keys) cudaFree(h.keys);
+        if (h.vals) cudaFree(h.vals);
+        if (h.temp) cudaFree(h.temp);
+        for (cudaEvent_t e : {h.up, h.sorted, h.down})
+            if (e) cudaEventDestroy(e);
+    }
+    for (cudaStream_t st : {s->hs_up, s->hs_sort, s->hs_down})
+        if (st) cudaStreamDestroy(st);
     for (cudaEvent_t e : s->ev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : s->seg_ev)
@@ -1090,6 +1110,62 @@ int thrs_sort_host(thrs_sorter* s, void* host_keys, void* host_values, uint32_t 
     CUDA_TRY(cudaMemcpyAsync(host_keys, s->ws_keys, kb, cudaMemcpyDeviceToHost, st), "D2H keys");
     if (pairs) CUDA_TRY(cudaMemcpyAsync(host_values, s->ws_vals, vb, cudaMemcpyDeviceToHost, st), "D2H values");
     CUDA_TRY(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+    return THRS_OK;
+}
+
+// Streaming form of thrs_sort_host for hosts that sort batch after batch: submit enqueues upload, sort and
+// download of one batch on three streams and returns; wait blocks until that batch is back in its host buffers.
+// With two or three slots in flight the upload of batch i+1 runs while batch i is sorted and batch i-1 is
+// downloaded, so a stream of sorts costs one PCIe direction per batch instead of two.
+int thrs_sort_host_submit(thrs_sorter* s, int slot, void* host_keys, void* host_values, uint32_t n, int start_bits, int end_bits)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host_submit: NULL sorter");
+    if (slot < 0 || slot >= THRS_HOST_SLOTS) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host_submit: slot out of range");
+    if (!host_keys && n) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host_submit: NULL keys");
+    std::lock_guard<std::mutex> lock(s->host_mu);
+    thrs_sorter::HostSlot& h = s->hslot[slot];
+    if (h.busy) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host_submit: slot in flight (thrs_sort_host_wait first)");
+    if (n == 0) return THRS_OK;
+    const bool pairs = host_values != nullptr;
+    thrs_temp_def def;
+    thrs_temp_bytes(s, n, &def);
+    const uint64_t kb = (uint64_t)s->kbytes * n, vb = (uint64_t)s->vbytes * n;
+    int rc;
+    if ((rc = grow(&h.keys, &h.keys_bytes, kb))) return rc;
+    if (pairs && (rc = grow(&h.vals, &h.vals_bytes, vb))) return rc;
+    if ((rc = grow(&h.temp, &h.temp_bytes, def.pSumBuffer + def.keyOutBuffer + (pairs ? def.valueOutBuffer : 0)))) return rc;
+    for (cudaStream_t* st : {&s->hs_up, &s->hs_sort, &s->hs_down})
+        if (!*st) CUDA_TRY(cudaStreamCreateWithFlags(st, cudaStreamNonBlocking), "cudaStreamCreate");
+    for (cudaEvent_t* e : {&h.up, &h.sorted, &h.down})
+        if (!*e) CUDA_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming), "cudaEventCreate");
+    CUDA_TRY(cudaMemcpyAsync(h.keys, host_keys, kb, cudaMemcpyHostToDevice, s->hs_up), "H2D keys");
+    if (pairs) CUDA_TRY(cudaMemcpyAsync(h.vals, host_values, vb, cudaMemcpyHostToDevice, s->hs_up), "H2D values");
+    CUDA_TRY(cudaEventRecord(h.up, s->hs_up), "cudaEventRecord");
+    CUDA_TRY(cudaStreamWaitEvent(s->hs_sort, h.up, 0), "cudaStreamWaitEvent");
+    rc = sort_impl(s, h.keys, pairs ? h.vals : nullptr, pairs, n, h.temp, start_bits, end_bits, s->hs_sort);
+    if (rc) return rc;
+    CUDA_TRY(cudaEventRecord(h.sorted, s->hs_sort), "cudaEventRecord");
+    CUDA_TRY(cudaStreamWaitEvent(s->hs_down, h.sorted, 0), "cudaStreamWaitEvent");
+    CUDA_TRY(cudaMemcpyAsync(host_keys, h.keys, kb, cudaMemcpyDeviceToHost, s->hs_down), "D2H keys");
+    if (pairs) CUDA_TRY(cudaMemcpyAsync(host_values, h.vals, vb, cudaMemcpyDeviceToHost, s->hs_down), "D2H values");
+    CUDA_TRY(cudaEventRecord(h.down, s->hs_down), "cudaEventRecord");
+    h.busy = true;
+    return THRS_OK;
+}
+
+int thrs_sort_host_wait(thrs_sorter* s, int slot)
+{
+    if (!s) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host_wait: NULL sorter");
+    if (slot < 0 || slot >= THRS_HOST_SLOTS) return fail(THRS_ERR_INVALID_ARGUMENT, "thrs_sort_host_wait: slot out of range");
+    cudaEvent_t done = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(s->host_mu);
+        if (!s->hslot[slot].busy) return THRS_OK;
+        done = s->hslot[slot].down;
+    }
+    CUDA_TRY(cudaEventSynchronize(done), "cudaEventSynchronize(download)");
+    std::lock_guard<std::mutex> lock(s->host_mu);
+    s->hslot[slot].busy = false;
     return THRS_OK;
 }
 

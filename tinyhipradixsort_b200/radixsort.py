@@ -288,6 +288,23 @@ class RadixSort:
             vp = host_values.ctypes.data if hasattr(host_values, "ctypes") else host_values.data_ptr()
         _check(self._lib.thrs_sort_host(self._h, kp, vp, n, int(startBits), int(endBits)))
 
+    HOST_SLOTS = 4  # THRS_HOST_SLOTS
+
+    def sortHostSubmit(self, slot, host_keys, host_values, startBits, endBits):
+        """Streaming form of sortHost: enqueue upload, sort and download of one batch in `slot` and return at once
+        (thrs_sort_host_submit).  The arrays (pinned CPU tensors for real overlap) are sorted in place once
+        sortHostWait(slot) has returned; up to HOST_SLOTS batches may be in flight."""
+        n = int(host_keys.shape[0])
+        kp = host_keys.ctypes.data if hasattr(host_keys, "ctypes") else host_keys.data_ptr()
+        vp = None
+        if host_values is not None:
+            vp = host_values.ctypes.data if hasattr(host_values, "ctypes") else host_values.data_ptr()
+        _check(self._lib.thrs_sort_host_submit(self._h, int(slot), kp, vp, n, int(startBits), int(endBits)))
+
+    def sortHostWait(self, slot):
+        """Block until the batch submitted in `slot` is back in its host arrays (thrs_sort_host_wait)."""
+        _check(self._lib.thrs_sort_host_wait(self._h, int(slot)))
+
     def profile(self, on):
         """Record CUDA events between the launches of each sort (thrs_profile_enable)."""
         _check(self._lib.thrs_profile_enable(self._h, int(bool(on))))
