@@ -116,6 +116,13 @@ int main(int argc, char** argv)
         for (int i = 0; i < 9; ++i) printf(" %s %.1f%%", names[i], 100.0 * ph[slot[i]] / tot);
         printf("\nlook-back (thread 0): resolves %llu, status re-polls %llu, prefix inside group %llu, group poll rounds %llu\n", ph[0], ph[1], ph[3], ph[4]);
     }
+    if (void* f = dlsym(RTLD_DEFAULT, "thrs_dev_check")) { // dev-only variant built with -DTHRS_PROTOCOL_CHECK
+        unsigned long long c[8];
+        ((void (*)(unsigned long long*, int))f)(c, 1);
+        printf("protocol check: double publish %llu, bad upgrade %llu, group overflow %llu, prefix conflict %llu, end-of-pass sum %llu, "
+               "dst out of range %llu, staging out of range %llu | tiles checked %llu (incl. thrs_create's ranking check)\n",
+               c[0], c[1], c[2], c[3], c[4], c[5], c[6], c[7]);
+    }
     if (void* f = dlsym(RTLD_DEFAULT, "thrs_dev_trace")) {
         static unsigned long long tr[6 * 32768];
         ((void (*)(unsigned long long*))f)(tr);

@@ -23,3 +23,16 @@ extern "C" __attribute__((visibility("default"))) void thrs_dev_trace(unsigned l
     cudaMemcpyFromSymbol(out, thrs_b200::g_trace, sizeof(unsigned long long) * 6 * 32768);
 }
 #endif
+
+#ifdef THRS_PROTOCOL_CHECK
+// dev build only: the violation counters of kernels.cuh (u32 instantiations), read and optionally cleared
+extern "C" __attribute__((visibility("default"))) void thrs_dev_check(unsigned long long* out, int reset)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, thrs_b200::g_check, sizeof(unsigned long long) * 8);
+    if (reset) {
+        unsigned long long z[8] = {};
+        cudaMemcpyToSymbol(thrs_b200::g_check, z, sizeof(z));
+    }
+}
+#endif

@@ -149,6 +149,62 @@ __device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v)
 // scheduled right away, and the successor does everything that does not depend on its predecessor's
 // output (shared-memory set-up, its first ticket) before it waits for the predecessor to complete
 // and flush.  Both instructions are no-ops in a launch without the attribute.
+// -DTHRS_PROTOCOL_CHECK (dev build, scripts/build_variant_u32.sh): the look-back / ticket protocol checks its own
+// invariants under production contention and counts violations (compute-sanitizer is closed on this pool; this is
+// the "asserts of your own" it asks for).  The product build compiles none of it.
+//   [0] a tile's status word was already published when its aggregate is written (a ticket handed out twice)
+//   [1] a tile's status word is not FLAG_AGGREGATE | count when its inclusive prefix replaces it
+//   [2] a group accumulator already holds GROUP_TILES arrivals when a tile adds its counts
+//   [3] a group prefix is republished with a DIFFERENT value
+//   [4] the last tile's inclusive prefix + count is not the end of the bin (look-back sums != global histogram;
+//       single-part launches: n < 2^30)
+//   [5] a scatter destination lies outside [0, n)     [6] a staging position lies outside the tile
+//   [7] tiles whose look-back was resolved under these checks (proof that the checks ran)
+#ifdef THRS_PROTOCOL_CHECK
+static __device__ unsigned long long g_check[8];
+#define PCHECK(cond, slot) do { if (cond) atomicAdd(&g_check[slot], 1ull); } while (0)
+#else
+#define PCHECK(cond, slot) do { } while (0)
+#endif
+// first publication of a tile's status word / upgrade to the inclusive prefix / group prefix / group arrival
+__device__ __forceinline__ void publish_aggregate(uint32_t* p, uint32_t v)
+{
+#ifdef THRS_PROTOCOL_CHECK
+    const uint32_t old = atomicExch(p, v);
+    PCHECK((old >> FLAG_SHIFT) != 0u, 0);
+#else
+    st_relaxed(p, v);
+#endif
+}
+__device__ __forceinline__ void publish_inclusive(uint32_t* p, uint32_t v, uint32_t count)
+{
+#ifdef THRS_PROTOCOL_CHECK
+    const uint32_t old = atomicExch(p, v);
+    PCHECK(old != (FLAG_AGGREGATE | count), 1);
+#else
+    (void)count;
+    st_relaxed(p, v);
+#endif
+}
+__device__ __forceinline__ void publish_group_prefix(uint32_t* p, uint32_t v)
+{
+#ifdef THRS_PROTOCOL_CHECK
+    const uint32_t old = atomicExch(p, v);
+    PCHECK(old != 0u && old != v, 3);
+#else
+    st_relaxed(p, v);
+#endif
+}
+__device__ __forceinline__ void add_group_arrival(uint32_t* p, uint32_t v)
+{
+#ifdef THRS_PROTOCOL_CHECK
+    const uint32_t old = atomicAdd(p, v);
+    PCHECK((old >> GROUP_SUM_BITS) >= (uint32_t)GROUP_TILES, 2);
+#else
+    atomicAdd(p, v);
+#endif
+}
+
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
@@ -705,8 +761,8 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
 #pragma unroll
             for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
             // early publication: successors can start summing while this tile still ranks
-            st_relaxed(my_status, (tile == t0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
-            atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
+            publish_aggregate(my_status, (tile == t0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+            add_group_arrival(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
         }
         bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
         if (tid < RADIX) {
@@ -759,6 +815,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
             pos = e.y + lower;
         }
         if (ok) {
+            PCHECK(pos >= (uint32_t)(THREADS * ITEMS), 6);
             if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
             else {
                 s_keys[pos] = key[j];
@@ -827,14 +884,16 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                     const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
                     if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
                 }
-                st_relaxed(gp + (size_t)g * RADIX, FLAG_PREFIX | pg); // helps the rest of this group and the next ones
+                publish_group_prefix(gp + (size_t)g * RADIX, FLAG_PREFIX | pg); // helps the rest of this group and the next ones
                 excl += pg;
             }
-            st_relaxed(my_status, FLAG_PREFIX | (excl + count));
+            publish_inclusive(my_status, FLAG_PREFIX | (excl + count), count);
         }
         const uint32_t gbase = base_in[(SEG ? seg_cur.seg * RADIX : 0u) + tid] + excl;
         s_off[tid] = gbase - bin_start;
         if (base_out != nullptr && last_tile) base_out[tid] = gbase + count;
+        if (!SEG && !PEER && base_out == nullptr && last_tile) PCHECK(gbase + count != (tid < RADIX - 1 ? base_in[tid + 1] : n), 4);
+        if (tid == 0) PCHECK(true, 7);
     }
     __syncthreads();
 
@@ -847,6 +906,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                 const uint2 kv = s_kv[p];
                 const uint32_t d = bin_or_digit<PEER, KIND, DESC>((KeyT)kv.x, bit, th);
                 const uint32_t dst = s_off[d] + p;
+                if (!SEG && !PEER) PCHECK(dst >= n, 5);
                 KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                 ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
                 ko[dst] = (KeyT)kv.x;
@@ -855,6 +915,7 @@ __device__ __forceinline__ uint32_t onesweep_tile(KeyT (&key)[ITEMS], const KeyT
                 const KeyT kk = s_keys[p];
                 const uint32_t d = bin_or_digit<PEER, KIND, DESC>(kk, bit, th);
                 const uint32_t dst = s_off[d] + p;
+                if (!SEG && !PEER) PCHECK(dst >= n, 5);
                 KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                 ko[dst] = kk;
                 if (PAIRS) {
@@ -1093,8 +1154,8 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
         if (cur && tid < RADIX) {
 #pragma unroll
             for (int w = 0; w < WARPS; ++w) count += tbl32[w * ROW + base_word(tid)];
-            st_relaxed(status + (size_t)tile * RADIX + tid, (tile == t0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
-            atomicAdd(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
+            publish_aggregate(status + (size_t)tile * RADIX + tid, (tile == t0 ? FLAG_PREFIX : FLAG_AGGREGATE) | count);
+            add_group_arrival(gsum + (size_t)(tile / GROUP_TILES) * RADIX + tid, (1u << GROUP_SUM_BITS) + count);
             TRACE(1, tile);
         }
         const uint32_t bin_start = block_exclusive_scan_256(tid < RADIX ? count : 0u, s_misc, nullptr);
@@ -1153,15 +1214,18 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                         const uint32_t a = ld_relaxed(gs + (size_t)(gg - 1) * RADIX);
                         if ((a >> GROUP_SUM_BITS) == (uint32_t)GROUP_TILES) { pg += a & GROUP_SUM_MASK; --gg; }
                     }
-                    st_relaxed(gp + (size_t)g * RADIX, FLAG_PREFIX | pg);
+                    publish_group_prefix(gp + (size_t)g * RADIX, FLAG_PREFIX | pg);
                     excl += pg;
                 }
-                st_relaxed(status + (size_t)p_tile * RADIX + tid, FLAG_PREFIX | (excl + p_count));
+                publish_inclusive(status + (size_t)p_tile * RADIX + tid, FLAG_PREFIX | (excl + p_count), p_count);
             }
             TRACE(5, p_tile);
             const uint32_t gbase = base_in[(SEG ? s_misc[ps + 1] * RADIX : 0u) + tid] + excl;
             s_off[tid] = gbase - p_bin_start;
             if (base_out != nullptr && p_tile == num_tiles - 1) base_out[tid] = gbase + p_count;
+            if (!SEG && !PEER && base_out == nullptr && p_tile == num_tiles - 1)
+                PCHECK(gbase + p_count != (tid < RADIX - 1 ? base_in[tid + 1] : n), 4);
+            if (tid == 0) PCHECK(true, 7);
             if (PEER && tid < 8) {
                 s_run[tid] = p_bin_start;
                 s_run[8 + tid] = p_count;
@@ -1216,6 +1280,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
 #endif
                     const uint32_t d = bin_or_digit<PEER, KIND, DESC>((KeyT)kv.x, bit, th);
                     const uint32_t dst = s_off[d] + p;
+                    if (!SEG && !PEER) PCHECK(dst >= n, 5);
                     KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                     ValT* vo = PEER ? reinterpret_cast<ValT*>(s_vptr[d]) : vals_out;
                     ko[dst] = (KeyT)kv.x;
@@ -1231,6 +1296,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
 #endif
                     const uint32_t d = bin_or_digit<PEER, KIND, DESC>(kk, bit, th);
                     const uint32_t dst = s_off[d] + p;
+                    if (!SEG && !PEER) PCHECK(dst >= n, 5);
                     KeyT* ko = PEER ? reinterpret_cast<KeyT*>(s_kptr[d]) : keys_out;
                     ko[dst] = kk;
 #ifdef THRS_DBL_STG
@@ -1296,6 +1362,7 @@ onesweep_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                     __syncwarp();
                     pos = e.y + lower;
                 }
+                PCHECK(pos >= (uint32_t)TILE, 6);
 #ifndef THRS_DBL_STAGE
                 if (PACKED) s_kv[pos] = make_uint2((uint32_t)key[j], val32(val[j]));
                 else {
