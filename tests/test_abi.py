@@ -147,3 +147,26 @@ def test_no_cpu_fallback_without_device():
     with pytest.raises(thrs.ThrsError):
         s.sortHostWait(thrs.RadixSort.HOST_SLOTS)  # slot out of range is rejected without a device, too
     s.sortHostWait(0)  # nothing in flight: returns
+
+
+def test_noalloc_entry_point_validates_without_a_device():
+    """thrs_sort_keys_noalloc: argument errors are reported before anything touches a device, and without a
+    device the call fails loudly like every other sort (no CPU fallback)."""
+    import torch
+
+    lib = _lib.load()
+    cfg = _lib.thrs_config()
+    lib.thrs_config_default(ctypes.byref(cfg))
+    h = ctypes.c_void_p()
+    assert lib.thrs_create(ctypes.byref(cfg), ctypes.byref(h)) == 0
+    try:
+        assert lib.thrs_sort_keys_noalloc(None, 4096, 16, 0, 32, None) == 1
+        assert lib.thrs_sort_keys_noalloc(h, 4096, 16, 0, 12, None) == 2      # hpp:856: multiple of 8
+        assert lib.thrs_sort_keys_noalloc(h, 4096, 16, 16, 8, None) == 2
+        assert lib.thrs_sort_keys_noalloc(h, 4096, (1 << 20) + 1, 0, 32, None) == 1
+        assert b"static scratch" in lib.thrs_last_error()
+        if not torch.cuda.is_available():
+            assert lib.thrs_sort_keys_noalloc(h, 4096, 16, 0, 32, None) in (1, 3, 4)  # never THRS_OK without a device
+            assert lib.thrs_last_error()
+    finally:
+        lib.thrs_destroy(h)
