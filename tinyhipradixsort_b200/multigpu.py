@@ -443,6 +443,42 @@ def verify_distributed(torch, dist, g, rk, rv, count, total):
     return bool(int(flag.item()))
 
 
+def _prefer_gpu_numa_node(torch, dev):
+    """Best effort, never raises: make this process's NEXT host allocations prefer the NUMA node its GPU hangs off
+    (set_mempolicy(MPOL_PREFERRED), which falls back to other nodes when that one is full), so that the pinned
+    slices of the end-to-end measurement do not all land on the node the launcher happens to run on.  Returns the
+    node, or None where the node is unknown (-1 in sysfs), the platform is not x86-64 Linux, or the call is refused."""
+    try:
+        import ctypes
+        import platform
+
+        if platform.system() != "Linux" or platform.machine() != "x86_64":
+            return None
+        p = torch.cuda.get_device_properties(dev)
+        bus = "%04x:%02x:%02x.0" % (int(p.pci_domain_id), int(p.pci_bus_id), int(p.pci_device_id))
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0 or node >= 64:
+            return None
+        libc = ctypes.CDLL(None, use_errno=True)
+        mask = ctypes.c_ulong(1 << node)
+        rc = libc.syscall(238, 1, ctypes.byref(mask), 65)  # SYS_set_mempolicy, MPOL_PREFERRED
+        return node if rc == 0 else None
+    except Exception:  # noqa: BLE001
+        return None
+
+
+def _default_numa_policy():
+    try:
+        import ctypes
+        import platform
+
+        if platform.system() == "Linux" and platform.machine() == "x86_64":
+            ctypes.CDLL(None, use_errno=True).syscall(238, 0, None, 0)  # MPOL_DEFAULT
+    except Exception:  # noqa: BLE001
+        pass
+
+
 def bench(args, dist, rank, world, dev, g):
     """bench.py at N > 1: the partitioned sort.  Weak scaling by default (`--log2n-per-gpu` pairs per
     GPU); `--log2n-total T` fixes the total instead (strong scaling; T = 32 is config C5)."""
@@ -543,10 +579,15 @@ def bench(args, dist, rank, world, dev, g):
 
     # end to end: pinned host slices in, sorted share out (H2D + sort + D2H inside the timed region)
     e2e_value, e2e_ms, e2e_note = None, None, None
+    numa_node = None
     if n_l <= (1 << 29):
+        # every rank's pinned slices on the NUMA node of ITS GPU where the host allows it (all ranks are started from
+        # one launcher, i.e. from one node's cores: with the default first-touch policy every slice would land there)
+        numa_node = _prefer_gpu_numa_node(torch, dev)
         hk0, hv0 = keys0.cpu().pin_memory(), vals0.cpu().pin_memory()
         hk_out = torch.empty(int(n_l * 1.06) + 8192, dtype=hk0.dtype).pin_memory()
         hv_out = torch.empty_like(hk_out).pin_memory()
+        _default_numa_policy()
         e2e = []
         for i in range(1 + max(1, min(args.steps, args.e2e_steps))):
             torch.cuda.synchronize()
@@ -614,7 +655,9 @@ def bench(args, dist, rank, world, dev, g):
                          "traffic": g["_traffic"](), "peak_source": peak_src, "bytes_per_launch": per_gpu_bytes,
                          "avg_launch_ms": avg_pass},
             "e2e": {"value": e2e_value, "unit": g["UNIT"], "h2d_bytes_per_step": total * 8, "d2h_bytes_per_step": total * 8,
-                    "ms_per_step": e2e_ms, "api": "DistributedRadixSort.sort_pairs (pinned host slices)", "note": e2e_note},
+                    "ms_per_step": e2e_ms, "api": "DistributedRadixSort.sort_pairs (pinned host slices)", "note": e2e_note,
+                    "host_memory_rank0": ("pinned, NUMA node %d preferred (the node of this rank's GPU)" % numa_node) if numa_node is not None
+                    else "pinned, default NUMA policy (GPU's node unknown or set_mempolicy refused)"},
             "gpu_launches": launches_per_step * args.steps * world,
             "clocks": clocks,
         }
