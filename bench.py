@@ -220,7 +220,10 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(times), "warmup": warmup, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": f"C2: stable sort of 2^{log2n} uniform-random u32 key + u32 value pairs on host cores, bits [0,32)",
+        "config": {"workload": (f"C2: stable sort of 2^{log2n} uniform-random u32 key + u32 value pairs on host cores, bits [0,32)"
+                                if args.gpus <= 1 else
+                                f"C5 shape: each step sorts a bounded sample (2^{log2n} pairs, one GPU's slice) of the {args.gpus} x 2^{args.log2n_per_gpu}"
+                                "-pair workload of the GPU arm on the host cores, bits [0,32); keys/s of a CPU sort falls slowly with n, so the sample flatters the CPU"),
                    "n_per_step": n, "bits": [0, 32]},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
